@@ -1,0 +1,802 @@
+// Rows A3 + A4 -- Encode-Process-Decode GraphNet on the 5th-generation tensor cores (tcgen05 + TMEM).
+//
+// Replaces EncProcDecGNN.forward / _process (gnn_manip/models/epd_gnn.py:86-105), EdgeModel / NodeModel /
+// InteractionNetwork.forward (deps/torch-graphnet/torch_graphnet/graph_networks.py:29-50, 63-85, 112-118),
+// the gathers nodes[idx] (utils/gn_utils.py:7-28) and scatter_sum (gn_utils.py:60-64) for hidden = 128,
+// num_layers = 2, LayerNorm -- the only configuration the reference instantiates (rollout_utils.py:133-134).
+//
+// Design
+//  * Every 128 x 128 x 128 GEMM of the MLPs is a tcgen05.mma chain (M = 128, N = 128, K = 16, kind::f16)
+//    with BF16 operands in shared memory (K-major, SWIZZLE_128B) and the fp32 accumulator in TMEM.
+//  * fp32 accuracy comes from a bf16x3 split: x = xh + xl, w = wh + wl, x.w ~= xh.wh + xh.wl + xl.wh
+//    (relative error ~2^-17 per product; measured 2e-5 on the accelerations vs 1e-2 for plain bf16 and
+//    1e-3 for tf32/fp16 -- the reference tolerance is 1e-3).  The three products accumulate in TMEM.
+//  * Weights are pre-packed once into the exact shared-memory image (hi + lo, swizzled) and streamed per
+//    layer with cp.async.bulk (TMA unit) onto an mbarrier while the previous layer's epilogue runs.
+//  * Edge MLP first layer is split algebraically: [e | v_recv | v_send] W1^T = e We^T + (v Wr^T)[recv] +
+//    (v Ws^T)[send]; the node kernel produces the two per-node projections, the edge epilogue gathers them.
+//  * Edges live in receiver-major order, so the scatter_add becomes a deterministic segmented sum done in
+//    the edge kernel's last epilogue out of shared memory (pre-residual LayerNorm output never touches HBM).
+//  * Epilogues own one accumulator row per thread (tcgen05.ld 32x32b): bias, ReLU, LayerNorm and the
+//    residual are thread-local; activations go back to shared memory as the next layer's A operand.
+#include "mp_tc.cuh"
+
+namespace gm {
+
+namespace {
+
+constexpr int NT = 256;                       // 8 warps: (lane quadrant q = warp & 3) x (column half = warp >> 2)
+constexpr uint32_t kIdesc = umma_idesc_bf16(kTile, kH);
+constexpr int kMiscBytes = 24 * 1024;
+constexpr int kMaxIn1 = 32;                   // widest SIMT first layer (encoders): node_dim / edge_dim <= 32
+
+struct Misc {                                 // lives after the operand buffers in dynamic smem
+  uint64_t bar_w;
+  uint64_t bar_mma[2];
+  uint32_t tmem_base;
+  uint32_t pad;
+  int recv[2][kTile];
+  int send[2][kTile];
+  float red[2][2][kTile];                     // [statistic][column half][row]
+  float dot[3][2][kTile];                     // decoder partial dot products
+  float b1[kH];
+  float w1[kH * kMaxIn1];                     // fp32 first-layer weights [128][in1]
+};
+static_assert(sizeof(Misc) <= kMiscBytes, "Misc overflows its shared-memory slot");
+
+struct Ctx {
+  char* a[2];          // generic pointers to the A operand buffers (hi image, lo image at +32 KB)
+  uint32_t a_s[2];     // shared-window addresses
+  uint32_t w_s;
+  Misc* misc;
+  uint32_t bar_w, bar_mma[2];
+  uint32_t tmem;
+  uint32_t ph_w, ph_mma[2];
+  int tid, lane, warp, q, hf, row;
+};
+
+__device__ __forceinline__ void ctx_init(Ctx& c, char* smem, int n_a, int tmem_cols) {
+  c.tid = threadIdx.x;
+  c.lane = c.tid & 31;
+  c.warp = c.tid >> 5;
+  c.q = c.warp & 3;
+  c.hf = c.warp >> 2;
+  c.row = c.q * 32 + c.lane;
+  char* base = (char*)(((uintptr_t)smem + 1023) & ~(uintptr_t)1023);
+  for (int i = 0; i < 2; ++i) {
+    c.a[i] = base + (size_t)(i < n_a ? i : 0) * kChunkBytes;
+    c.a_s[i] = smem_u32(c.a[i]);
+  }
+  char* w = base + (size_t)n_a * kChunkBytes;
+  c.w_s = smem_u32(w);
+  c.misc = reinterpret_cast<Misc*>(w + kChunkBytes);
+  c.bar_w = smem_u32(&c.misc->bar_w);
+  c.bar_mma[0] = smem_u32(&c.misc->bar_mma[0]);
+  c.bar_mma[1] = smem_u32(&c.misc->bar_mma[1]);
+  c.ph_w = 0;
+  c.ph_mma[0] = c.ph_mma[1] = 0;
+  if (c.tid == 0) {
+    mbar_init(c.bar_w, 1);
+    mbar_init(c.bar_mma[0], 1);
+    mbar_init(c.bar_mma[1], 1);
+    fence_mbar_init();
+  }
+  if (c.warp == 0) {
+    tmem_alloc(smem_u32(&c.misc->tmem_base), (uint32_t)tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  c.tmem = c.misc->tmem_base;
+}
+
+__device__ __forceinline__ void ctx_fini(Ctx& c, int tmem_cols) {
+  tc_fence_before();
+  __syncthreads();
+  if (c.warp == 0) tmem_dealloc(c.tmem, (uint32_t)tmem_cols);
+}
+
+// thread 0: stream one packed weight chunk (64 KB) into the W buffer; completion on bar_w.
+__device__ __forceinline__ void load_w(const Ctx& c, const void* chunk) {
+  if (c.tid == 0) {
+    mbar_expect_tx(c.bar_w, kChunkBytes);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      bulk_g2s(c.w_s + i * kKBlockBytes, (const char*)chunk + (size_t)i * kKBlockBytes, kKBlockBytes, c.bar_w);
+  }
+  __syncwarp();
+}
+
+// thread 0: D[tmem_d] (+)= A x W^T with the bf16x3 split; 8 K-steps x 3 products.
+__device__ __forceinline__ void issue_mma(uint32_t a_s, uint32_t w_s, uint32_t tmem_d, bool accumulate) {
+#pragma unroll
+  for (int kb = 0; kb < 2; ++kb) {
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+      const uint32_t off = kb * kKBlockBytes + ks * 32;
+      const uint64_t ah = umma_desc_sw128(a_s + off), al = umma_desc_sw128(a_s + kImageBytes + off);
+      const uint64_t wh = umma_desc_sw128(w_s + off), wl = umma_desc_sw128(w_s + kImageBytes + off);
+      umma_bf16_ss(tmem_d, ah, wh, kIdesc, (accumulate || kb || ks) ? 1u : 0u);
+      umma_bf16_ss(tmem_d, ah, wl, kIdesc, 1u);
+      umma_bf16_ss(tmem_d, al, wh, kIdesc, 1u);
+    }
+  }
+}
+
+// All threads call.  Publishes generic-proxy smem writes (A operand) to the tensor core, then thread 0 waits for
+// the weights and issues the MMA chain for `n_sub` accumulators (sub s uses A buffer a_idx0+s, TMEM cols s*128).
+__device__ __forceinline__ void launch_gemm(Ctx& c, int a_idx0, int n_sub, bool accumulate) {
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  if (c.tid == 0) {
+    mbar_wait(c.bar_w, c.ph_w);
+    tc_fence_after();
+    for (int s = 0; s < n_sub; ++s) {
+      issue_mma(c.a_s[a_idx0 + s], c.w_s, c.tmem + s * kH, accumulate);
+      umma_commit(c.bar_mma[s]);
+    }
+  }
+  __syncwarp();   // re-converge warp 0 before the .sync.aligned TMEM loads that follow
+  c.ph_w ^= 1;
+}
+__device__ __forceinline__ void wait_gemm(Ctx& c, int s) {
+  mbar_wait(c.bar_mma[s], c.ph_mma[s]);
+  c.ph_mma[s] ^= 1;
+  tc_fence_after();
+}
+
+// byte offset of logical (row, col8-group) inside a SWIZZLE_128B K-major bf16 image
+__device__ __forceinline__ uint32_t a_off(int row, int col) {
+  const int kb = col >> 6, chunk = (col & 63) >> 3;
+  return kb * kKBlockBytes + row * 128 + ((chunk ^ (row & 7)) << 4) + ((col & 7) << 1);
+}
+
+// write 8 consecutive fp32 activations (cols col..col+7 of `row`) as bf16 hi / lo operand data
+__device__ __forceinline__ void store_a8(char* a, int row, int col, const float* v) {
+  uint4 hi, lo;
+  split_bf16x2(v[0], v[1], hi.x, lo.x);
+  split_bf16x2(v[2], v[3], hi.y, lo.y);
+  split_bf16x2(v[4], v[5], hi.z, lo.z);
+  split_bf16x2(v[6], v[7], hi.w, lo.w);
+  const uint32_t o = a_off(row, col);
+  *reinterpret_cast<uint4*>(a + o) = hi;
+  *reinterpret_cast<uint4*>(a + kImageBytes + o) = lo;
+}
+
+// Cooperative tile load: 128 fp32 rows (row stride 128 floats, optional row index map) -> bf16x2 operand.
+// Warp per row, lane owns 4 consecutive columns (coalesced 512 B per row).
+template <typename RowPtr>
+__device__ __forceinline__ void load_rows_to_a(const Ctx& c, char* a, int rows_valid, RowPtr rowptr) {
+#pragma unroll 4
+  for (int r = c.warp; r < kTile; r += NT / 32) {
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < rows_valid) x = __ldg(reinterpret_cast<const float4*>(rowptr(r)) + c.lane);
+    uint2 hi, lo;
+    split_bf16x2(x.x, x.y, hi.x, lo.x);
+    split_bf16x2(x.z, x.w, hi.y, lo.y);
+    const uint32_t o = a_off(r, 4 * c.lane);
+    *reinterpret_cast<uint2*>(a + o) = hi;
+    *reinterpret_cast<uint2*>(a + kImageBytes + o) = lo;
+  }
+}
+
+__device__ __forceinline__ uint32_t d_addr(const Ctx& c, int sub, int col) {
+  return c.tmem + ((uint32_t)(c.q * 32) << 16) + (uint32_t)(sub * kH + col);
+}
+
+// Hidden-layer epilogue: A[a_idx] <- split(relu(D + bias (+ addA[row] + addB[row]))).
+__device__ __forceinline__ void epi_hidden(const Ctx& c, int sub, int a_idx, const float* __restrict__ bias,
+                                           const float* __restrict__ add_a, const float* __restrict__ add_b) {
+#pragma unroll 1
+  for (int h = 0; h < 2; ++h) {
+    const int col0 = c.hf * 64 + h * 32;
+    float v[32];
+    tmem_ld32(d_addr(c, sub, col0), v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(bias + col0) + j);
+      v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+    }
+    if (add_a != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 x = __ldg(reinterpret_cast<const float4*>(add_a + col0) + j);
+        const float4 y = __ldg(reinterpret_cast<const float4*>(add_b + col0) + j);
+        v[4 * j] += x.x + y.x; v[4 * j + 1] += x.y + y.y; v[4 * j + 2] += x.z + y.z; v[4 * j + 3] += x.w + y.w;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) store_a8(c.a[a_idx], c.row, col0 + 8 * g, v + 8 * g);
+  }
+}
+
+// LayerNorm statistics of this thread's accumulator row (D + bias), over all 128 columns.
+// Two-pass (mean, then centred second moment) with the two column halves combined through smem.
+__device__ __forceinline__ void ln_stats(const Ctx& c, int sub, const float* __restrict__ bias, float& mean,
+                                         float& rstd) {
+  float s = 0.f;
+#pragma unroll 1
+  for (int h = 0; h < 2; ++h) {
+    const int col0 = c.hf * 64 + h * 32;
+    float v[32];
+    tmem_ld32(d_addr(c, sub, col0), v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) s += v[j] + __ldg(bias + col0 + j);
+  }
+  c.misc->red[0][c.hf][c.row] = s;
+  __syncthreads();
+  mean = (c.misc->red[0][0][c.row] + c.misc->red[0][1][c.row]) * (1.0f / kH);
+  float ss = 0.f;
+#pragma unroll 1
+  for (int h = 0; h < 2; ++h) {
+    const int col0 = c.hf * 64 + h * 32;
+    float v[32];
+    tmem_ld32(d_addr(c, sub, col0), v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float d = v[j] + __ldg(bias + col0 + j) - mean;
+      ss = fmaf(d, d, ss);
+    }
+  }
+  c.misc->red[1][c.hf][c.row] = ss;
+  __syncthreads();
+  const float var = (c.misc->red[1][0][c.row] + c.misc->red[1][1][c.row]) * (1.0f / kH);
+  rstd = 1.0f / sqrtf(var + 1e-5f);
+}
+
+// y[j] = LN(D + bias)[col0 + j] for 32 columns
+__device__ __forceinline__ void ln_apply32(const Ctx& c, int sub, int col0, const float* __restrict__ bias,
+                                           const float* __restrict__ g, const float* __restrict__ b, float mean,
+                                           float rstd, float* v) {
+  tmem_ld32(d_addr(c, sub, col0), v);
+  tmem_ld_wait();
+#pragma unroll
+  for (int j = 0; j < 32; ++j)
+    v[j] = (v[j] + __ldg(bias + col0 + j) - mean) * rstd * __ldg(g + col0 + j) + __ldg(b + col0 + j);
+}
+
+// fp32 staging tile [128][128] with the float4-chunk index XOR-swizzled by (row & 7): conflict-free both for
+// row-owner float4 writes and for column-owner scalar reads.
+__device__ __forceinline__ uint32_t s_off(int row, int col) {
+  return (uint32_t)row * 512u + ((((uint32_t)col >> 2) ^ ((uint32_t)row & 7u)) << 4) + (((uint32_t)col & 3u) << 2);
+}
+
+// ================================================================================================
+// mp_edge: one message-passing step, edge half, for 2 x 128 edges per CTA iteration.
+// ================================================================================================
+__global__ void __launch_bounds__(NT, 1) mp_edge_kernel(TcMlp m, TcGraph g, TcBuffers b) {
+  extern __shared__ char smem_raw[];
+  Ctx c;
+  ctx_init(c, smem_raw, 2, 256);
+  const int E = min(*g.n_edges_dev, g.max_edges);
+  const int n_tiles = (E + 2 * kTile - 1) / (2 * kTile);
+
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int row0 = tile * 2 * kTile;
+    load_w(c, m.wc[0]);
+    // ---- prologue: ids + e tile -> A operands ----
+    for (int i = c.tid; i < 2 * kTile; i += NT) {
+      const int s = i >> 7, r = i & (kTile - 1), ge = row0 + i;
+      c.misc->recv[s][r] = ge < E ? g.erecv[ge] : -1;
+      c.misc->send[s][r] = ge < E ? g.esend[ge] : -1;
+    }
+#pragma unroll 1
+    for (int s = 0; s < 2; ++s) {
+      const int base = row0 + s * kTile;
+      const float* e_in = b.e;
+      load_rows_to_a(c, c.a[s], min(kTile, max(E - base, 0)),
+                     [=](int r) { return e_in + (size_t)(base + r) * kH; });
+    }
+    // ---- layer 1: e We^T + Pr[recv] + Ps[send] + b1 ----
+    launch_gemm(c, 0, 2, false);
+#pragma unroll 1
+    for (int s = 0; s < 2; ++s) {
+      wait_gemm(c, s);
+      if (s == 1) load_w(c, m.wc[1]);
+      const int rid = c.misc->recv[s][c.row], sid = c.misc->send[s][c.row];
+      const float* pa = b.pr + (size_t)(rid < 0 ? 0 : rid) * kH;
+      const float* pb = b.ps + (size_t)(sid < 0 ? 0 : sid) * kH;
+      epi_hidden(c, s, s, m.b1, pa, pb);
+    }
+    // ---- layer 2 ----
+    launch_gemm(c, 0, 2, false);
+#pragma unroll 1
+    for (int s = 0; s < 2; ++s) {
+      wait_gemm(c, s);
+      if (s == 1) load_w(c, m.wc[2]);
+      epi_hidden(c, s, s, m.b2, nullptr, nullptr);
+    }
+    // ---- layer 3 + LayerNorm + residual + receiver-segmented sum ----
+    launch_gemm(c, 0, 2, false);
+#pragma unroll 1
+    for (int s = 0; s < 2; ++s) {
+      wait_gemm(c, s);
+      const int base = row0 + s * kTile;
+      const int rows_valid = min(kTile, max(E - base, 0));
+      float mean, rstd;
+      ln_stats(c, s, m.b3, mean, rstd);
+      char* stage = c.a[s];                      // A[s] is free: its last reader (layer-3 MMA) completed
+      const size_t grow = (size_t)(base + c.row) * kH;
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        const int col0 = c.hf * 64 + h * 32;
+        float v[32];
+        ln_apply32(c, s, col0, m.b3, m.ln_g, m.ln_b, mean, rstd, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(stage + s_off(c.row, col0 + 4 * j)) =
+              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        if (c.row < rows_valid) {                // e' = LN(...) + e   (epd_gnn.py:104), in place
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4* p = reinterpret_cast<float4*>(b.e + grow + col0) + j;
+            float4 o = *p;
+            o.x += v[4 * j]; o.y += v[4 * j + 1]; o.z += v[4 * j + 2]; o.w += v[4 * j + 3];
+            *p = o;
+          }
+        }
+      }
+      __syncthreads();
+      // column-owner pass: thread = (64-row agg tile, column); rows of one receiver are contiguous
+      {
+        const int half = c.tid >> 7, col = c.tid & (kH - 1);
+        const int rb = half * kAggRows, re = min(rb + kAggRows, rows_valid);
+        if (rb < re) {
+          const int* rv = c.misc->recv[s];
+          int cur = rv[rb];
+          bool cont = (base + rb) > g.recv_ptr[cur];     // segment began in an earlier agg tile
+          float acc = 0.f;
+          const size_t agg_tile = (size_t)(base + rb) / kAggRows;
+          for (int r = rb; r < re; ++r) {
+            const int rr = rv[r];
+            if (rr != cur) {
+              if (cont) b.carry[agg_tile * kH + col] = acc; else b.aggpart[(size_t)cur * kH + col] = acc;
+              cont = false; acc = 0.f; cur = rr;
+            }
+            acc += *reinterpret_cast<const float*>(stage + s_off(r, col));
+          }
+          if (cont) b.carry[agg_tile * kH + col] = acc; else b.aggpart[(size_t)cur * kH + col] = acc;
+        }
+      }
+      __syncthreads();                            // staging reads done before the next prologue rewrites A[s]
+    }
+  }
+  ctx_fini(c, 256);
+}
+
+// ================================================================================================
+// Shared tail of the node kernels: v' (already split into A[0]) -> Pr, Ps of the next edge MLP, or decoder.
+// ================================================================================================
+__device__ __forceinline__ void store_d_rows(const Ctx& c, int sub, float* __restrict__ out, int node0,
+                                             int rows_valid) {
+#pragma unroll 1
+  for (int h = 0; h < 2; ++h) {
+    const int col0 = c.hf * 64 + h * 32;
+    float v[32];
+    tmem_ld32(d_addr(c, sub, col0), v);
+    tmem_ld_wait();
+    if (c.row < rows_valid) {
+      float4* p = reinterpret_cast<float4*>(out + (size_t)(node0 + c.row) * kH + col0);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) p[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+  }
+}
+
+// expects: load_w(next chunk 0) already issued, A[0] holds split(v').
+__device__ __forceinline__ void node_tail(Ctx& c, const TcMlp* next_edge, const TcMlp* dec, int out_dim,
+                                          float* __restrict__ pred, const TcBuffers& b, int node0, int rows_valid) {
+  if (dec == nullptr) {
+    // Pr = v' Wr^T, Ps = v' Ws^T  (receiver / sender blocks of the next phi_edge first layer)
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    load_w(c, next_edge->wc[4]);
+    store_d_rows(c, 0, b.pr, node0, rows_valid);
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    store_d_rows(c, 0, b.ps, node0, rows_valid);
+  } else {
+    // decoder: Linear+ReLU, Linear+ReLU on the tensor cores, Linear(128 -> out_dim) with CUDA cores
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    load_w(c, dec->wc[1]);
+    epi_hidden(c, 0, 0, dec->b1, nullptr, nullptr);
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    float acc[3] = {0.f, 0.f, 0.f};
+#pragma unroll 1
+    for (int h = 0; h < 2; ++h) {
+      const int col0 = c.hf * 64 + h * 32;
+      float v[32];
+      tmem_ld32(d_addr(c, 0, col0), v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float x = fmaxf(v[j] + __ldg(dec->b2 + col0 + j), 0.f);
+#pragma unroll
+        for (int o = 0; o < 3; ++o)
+          if (o < out_dim) acc[o] = fmaf(x, __ldg(dec->w3 + o * kH + col0 + j), acc[o]);
+      }
+    }
+#pragma unroll
+    for (int o = 0; o < 3; ++o) c.misc->dot[o][c.hf][c.row] = acc[o];
+    __syncthreads();
+    if (c.hf == 0 && c.row < rows_valid) {
+      for (int o = 0; o < out_dim; ++o)
+        pred[(size_t)(node0 + c.row) * out_dim + o] =
+            c.misc->dot[o][0][c.row] + c.misc->dot[o][1][c.row] + __ldg(dec->b3 + o);
+    }
+    __syncthreads();
+  }
+}
+
+// layers 2,3 + LayerNorm (+ residual) of a node MLP whose layer-1 pre-activation sits in D[0];
+// leaves v' in global memory and split(v') in A[0]; issues the load of `next_chunk`.
+__device__ __forceinline__ void node_body(Ctx& c, const TcMlp& m, const void* next_chunk, bool residual,
+                                          const TcBuffers& b, int node0, int rows_valid) {
+  load_w(c, m.wc[2]);
+  epi_hidden(c, 0, 0, m.b1, nullptr, nullptr);
+  launch_gemm(c, 0, 1, false);
+  wait_gemm(c, 0);
+  load_w(c, m.wc[3]);
+  epi_hidden(c, 0, 0, m.b2, nullptr, nullptr);
+  launch_gemm(c, 0, 1, false);
+  wait_gemm(c, 0);
+  load_w(c, next_chunk);
+  float mean, rstd;
+  ln_stats(c, 0, m.b3, mean, rstd);
+  const size_t grow = (size_t)(node0 + c.row) * kH;
+#pragma unroll 1
+  for (int h = 0; h < 2; ++h) {
+    const int col0 = c.hf * 64 + h * 32;
+    float v[32];
+    ln_apply32(c, 0, col0, m.b3, m.ln_g, m.ln_b, mean, rstd, v);
+    if (c.row < rows_valid) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float4* p = reinterpret_cast<float4*>(b.v + grow + col0) + j;
+        if (residual) {                         // v' = LN(...) + v   (epd_gnn.py:103), in place
+          const float4 o = *p;
+          v[4 * j] += o.x; v[4 * j + 1] += o.y; v[4 * j + 2] += o.z; v[4 * j + 3] += o.w;
+        }
+        *p = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = 0.f;
+    }
+#pragma unroll
+    for (int gq = 0; gq < 4; ++gq) store_a8(c.a[0], c.row, col0 + 8 * gq, v + 8 * gq);
+  }
+}
+
+// ================================================================================================
+// mp_node: node half of a message-passing step for 128 nodes per CTA iteration.
+// chunks: wc[0] = W1[:, 0:128] (aggregated edges), wc[1] = W1[:, 128:256] (node), wc[2], wc[3].
+// ================================================================================================
+__global__ void __launch_bounds__(NT, 1)
+mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict__ pred, TcGraph g, TcBuffers b) {
+  extern __shared__ char smem_raw[];
+  Ctx c;
+  ctx_init(c, smem_raw, 2, 128);
+  const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int node0 = tile * kTile;
+    const int rows_valid = min(kTile, g.n_nodes - node0);
+    load_w(c, m.wc[0]);
+    // A[0] <- total aggregate per node = first-tile partial + carries of the following agg tiles
+#pragma unroll 2
+    for (int r = c.warp; r < kTile; r += NT / 32) {
+      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r < rows_valid) {
+        const int n = node0 + r;
+        const int sb = g.recv_ptr[n], se = g.recv_ptr[n + 1];
+        if (se > sb) {
+          x = __ldg(reinterpret_cast<const float4*>(b.aggpart + (size_t)n * kH) + c.lane);
+          const int t0 = sb / kAggRows, t1 = (se - 1) / kAggRows;
+          for (int t = t0 + 1; t <= t1; ++t) {
+            const float4 y = __ldg(reinterpret_cast<const float4*>(b.carry + (size_t)t * kH) + c.lane);
+            x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+          }
+        }
+      }
+      uint2 hi, lo;
+      split_bf16x2(x.x, x.y, hi.x, lo.x);
+      split_bf16x2(x.z, x.w, hi.y, lo.y);
+      const uint32_t o = a_off(r, 4 * c.lane);
+      *reinterpret_cast<uint2*>(c.a[0] + o) = hi;
+      *reinterpret_cast<uint2*>(c.a[0] + kImageBytes + o) = lo;
+    }
+    {
+      const float* v_in = b.v;
+      load_rows_to_a(c, c.a[1], rows_valid, [=](int r) { return v_in + (size_t)(node0 + r) * kH; });
+    }
+    launch_gemm(c, 0, 1, false);     // agg @ W1a^T
+    wait_gemm(c, 0);
+    load_w(c, m.wc[1]);
+    launch_gemm(c, 1, 1, true);      // + v @ W1b^T   (A[1], same accumulator)
+    // note: launch_gemm(c, 1, ...) maps sub 0 -> A[1], TMEM cols 0
+    wait_gemm(c, 0);
+    node_body(c, m, has_dec ? next.wc[0] : next.wc[3], true, b, node0, rows_valid);
+    node_tail(c, &next, has_dec ? &next : nullptr, out_dim, pred, b, node0, rows_valid);
+  }
+  ctx_fini(c, 128);
+}
+
+// ================================================================================================
+// enc_node: node encoder (Linear(node_dim,128) on CUDA cores, then tensor cores) + Pr/Ps of step 0.
+// ================================================================================================
+__global__ void __launch_bounds__(NT, 1)
+enc_node_kernel(TcMlp m, TcMlp next, int node_dim, const float* __restrict__ nodes, TcGraph g, TcBuffers b) {
+  extern __shared__ char smem_raw[];
+  Ctx c;
+  ctx_init(c, smem_raw, 1, 128);
+  for (int i = c.tid; i < kH * node_dim; i += NT) c.misc->w1[i] = m.w1[i];
+  for (int i = c.tid; i < kH; i += NT) c.misc->b1[i] = m.b1[i];
+  __syncthreads();
+  const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int node0 = tile * kTile;
+    const int rows_valid = min(kTile, g.n_nodes - node0);
+    load_w(c, m.wc[2]);
+    float x[kMaxIn1];
+#pragma unroll
+    for (int k = 0; k < kMaxIn1; ++k)
+      x[k] = (k < node_dim && c.row < rows_valid) ? __ldg(nodes + (size_t)(node0 + c.row) * node_dim + k) : 0.f;
+#pragma unroll 1
+    for (int g8 = 0; g8 < 8; ++g8) {
+      const int col0 = c.hf * 64 + g8 * 8;
+      float h[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float acc = c.misc->b1[col0 + j];
+        const float* w = c.misc->w1 + (size_t)(col0 + j) * node_dim;
+#pragma unroll
+        for (int k = 0; k < kMaxIn1; ++k)
+          if (k < node_dim) acc = fmaf(x[k], w[k], acc);
+        h[j] = fmaxf(acc, 0.f);
+      }
+      store_a8(c.a[0], c.row, col0, h);
+    }
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    load_w(c, m.wc[3]);
+    epi_hidden(c, 0, 0, m.b2, nullptr, nullptr);
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    load_w(c, next.wc[3]);
+    float mean, rstd;
+    ln_stats(c, 0, m.b3, mean, rstd);
+    const size_t grow = (size_t)(node0 + c.row) * kH;
+#pragma unroll 1
+    for (int hh = 0; hh < 2; ++hh) {
+      const int col0 = c.hf * 64 + hh * 32;
+      float v[32];
+      ln_apply32(c, 0, col0, m.b3, m.ln_g, m.ln_b, mean, rstd, v);
+      if (c.row < rows_valid) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          reinterpret_cast<float4*>(b.v + grow + col0)[j] =
+              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+      }
+#pragma unroll
+      for (int gq = 0; gq < 4; ++gq) store_a8(c.a[0], c.row, col0 + 8 * gq, v + 8 * gq);
+    }
+    node_tail(c, &next, nullptr, 0, nullptr, b, node0, rows_valid);
+  }
+  ctx_fini(c, 128);
+}
+
+// ================================================================================================
+// enc_edge: edge encoder.  Edge features are built on the fly from positions (row A2) unless an explicit
+// edge_attr tensor is given; Linear(edge_dim,128) on CUDA cores, then two tensor-core layers + LayerNorm.
+// ================================================================================================
+__global__ void __launch_bounds__(NT, 1)
+enc_edge_kernel(TcMlp m, int edge_dim, const float* __restrict__ pos, int pos_stride, float conn_r,
+                const float* __restrict__ edge_attr, const int* __restrict__ eref, TcGraph g, TcBuffers b) {
+  extern __shared__ char smem_raw[];
+  Ctx c;
+  ctx_init(c, smem_raw, 1, 128);
+  for (int i = c.tid; i < kH * edge_dim; i += NT) c.misc->w1[i] = m.w1[i];
+  for (int i = c.tid; i < kH; i += NT) c.misc->b1[i] = m.b1[i];
+  __syncthreads();
+  const int E = min(*g.n_edges_dev, g.max_edges);
+  const int n_tiles = (E + kTile - 1) / kTile;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int row0 = tile * kTile;
+    const int rows_valid = min(kTile, E - row0);
+    load_w(c, m.wc[2]);
+    float x[kMaxIn1];
+#pragma unroll
+    for (int k = 0; k < kMaxIn1; ++k) x[k] = 0.f;
+    if (c.row < rows_valid) {
+      const int ge = row0 + c.row;
+      if (edge_attr != nullptr) {
+        const float* src = edge_attr + (size_t)(eref ? eref[ge] : ge) * edge_dim;
+#pragma unroll
+        for (int k = 0; k < kMaxIn1; ++k)
+          if (k < edge_dim) x[k] = __ldg(src + k);
+      } else {
+        const float4 f = edge_feature(pos, pos_stride, g.esend[ge], g.erecv[ge], conn_r);
+        x[0] = f.x; x[1] = f.y; x[2] = f.z; x[3] = f.w;
+      }
+    }
+#pragma unroll 1
+    for (int g8 = 0; g8 < 8; ++g8) {
+      const int col0 = c.hf * 64 + g8 * 8;
+      float h[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float acc = c.misc->b1[col0 + j];
+        const float* w = c.misc->w1 + (size_t)(col0 + j) * edge_dim;
+#pragma unroll
+        for (int k = 0; k < kMaxIn1; ++k)
+          if (k < edge_dim) acc = fmaf(x[k], w[k], acc);
+        h[j] = fmaxf(acc, 0.f);
+      }
+      store_a8(c.a[0], c.row, col0, h);
+    }
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    load_w(c, m.wc[3]);
+    epi_hidden(c, 0, 0, m.b2, nullptr, nullptr);
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    float mean, rstd;
+    ln_stats(c, 0, m.b3, mean, rstd);
+    const size_t grow = (size_t)(row0 + c.row) * kH;
+#pragma unroll 1
+    for (int hh = 0; hh < 2; ++hh) {
+      const int col0 = c.hf * 64 + hh * 32;
+      float v[32];
+      ln_apply32(c, 0, col0, m.b3, m.ln_g, m.ln_b, mean, rstd, v);
+      if (c.row < rows_valid) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          reinterpret_cast<float4*>(b.e + grow + col0)[j] =
+              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      }
+    }
+    __syncthreads();   // all TMEM reads of this tile retire before the next tile's MMA overwrites D
+  }
+  ctx_fini(c, 128);
+}
+
+// ---- weight packing: fp32 [128][ld] block -> bf16 hi/lo swizzled operand images ----
+__global__ void pack_chunk_kernel(const float* __restrict__ w, int ld, int col0, char* __restrict__ chunk) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // one thread per (row n, 8-column group)
+  if (idx >= kH * (kH / 8)) return;
+  const int n = idx / (kH / 8), c8 = (idx % (kH / 8)) * 8;
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = w[(size_t)n * ld + col0 + c8 + j];
+  store_a8(chunk, n, c8, v);
+}
+
+// ---- self-test GEMM: out = x @ W^T through exactly the operand path the MLP kernels use ----
+__global__ void __launch_bounds__(NT, 1)
+selftest_gemm_kernel(const float* __restrict__ x, const void* chunk, float* __restrict__ out, int M) {
+  extern __shared__ char smem_raw[];
+  Ctx c;
+  ctx_init(c, smem_raw, 1, 128);
+  const int n_tiles = M / kTile;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int row0 = tile * kTile;
+    load_w(c, chunk);
+    load_rows_to_a(c, c.a[0], kTile, [=](int r) { return x + (size_t)(row0 + r) * kH; });
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    store_d_rows(c, 0, out, row0, kTile);
+    __syncthreads();
+  }
+  ctx_fini(c, 128);
+}
+
+size_t smem_bytes(int n_a) { return (size_t)n_a * kChunkBytes + kChunkBytes + kMiscBytes + 1024; }
+
+template <typename Kern>
+int set_smem(Kern kern, size_t bytes) {
+  GM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return GM_OK;
+}
+
+}  // namespace
+
+// opt in to the large dynamic shared-memory carve-outs once per process (outside any stream capture)
+int tc_configure() {
+  static bool done = false;
+  if (done) return GM_OK;
+  int rc;
+  if ((rc = set_smem(mp_edge_kernel, smem_bytes(2)))) return rc;
+  if ((rc = set_smem(mp_node_kernel, smem_bytes(2)))) return rc;
+  if ((rc = set_smem(enc_node_kernel, smem_bytes(1)))) return rc;
+  if ((rc = set_smem(enc_edge_kernel, smem_bytes(1)))) return rc;
+  if ((rc = set_smem(selftest_gemm_kernel, smem_bytes(1)))) return rc;
+  done = true;
+  return GM_OK;
+}
+
+int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_t stream) {
+  if (g.max_edges <= 0) return GM_OK;
+  const size_t sm = smem_bytes(2);
+  int rc = tc_configure();
+  if (rc) return rc;
+  const int grid = min(ceil_div(g.max_edges, 2 * kTile), kNumSMs);
+  mp_edge_kernel<<<grid, NT, sm, stream>>>(m, g, b);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("mp_edge_kernel");
+  return GM_OK;
+}
+
+int tc_mp_node(const TcMlp& m, const TcMlp* next_edge, const TcMlp* dec, int out_dim, float* pred,
+               const TcGraph& g, const TcBuffers& b, cudaStream_t stream) {
+  GM_REQUIRE((next_edge != nullptr) != (dec != nullptr), "tc_mp_node: exactly one of next_edge / dec");
+  GM_REQUIRE(dec == nullptr || (out_dim >= 1 && out_dim <= 3), "tc_mp_node: out_dim=%d outside [1,3]", out_dim);
+  const size_t sm = smem_bytes(2);
+  int rc = tc_configure();
+  if (rc) return rc;
+  const int grid = min(ceil_div(g.n_nodes, kTile), kNumSMs);
+  mp_node_kernel<<<grid, NT, sm, stream>>>(m, dec ? *dec : *next_edge, dec ? 1 : 0, out_dim, pred, g, b);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("mp_node_kernel");
+  return GM_OK;
+}
+
+int tc_enc_node(const TcMlp& m, const TcMlp& next_edge, int node_dim, const float* nodes, const TcGraph& g,
+                const TcBuffers& b, cudaStream_t stream) {
+  GM_REQUIRE(node_dim >= 1 && node_dim <= kMaxIn1, "tc_enc_node: node_dim=%d outside [1,%d]", node_dim, kMaxIn1);
+  const size_t sm = smem_bytes(1);
+  int rc = tc_configure();
+  if (rc) return rc;
+  const int grid = min(ceil_div(g.n_nodes, kTile), kNumSMs);
+  enc_node_kernel<<<grid, NT, sm, stream>>>(m, next_edge, node_dim, nodes, g, b);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("enc_node_kernel");
+  return GM_OK;
+}
+
+int tc_enc_edge(const TcMlp& m, int edge_dim, const float* pos, int pos_stride, float conn_r,
+                const float* edge_attr, const int* eref, const TcGraph& g, const TcBuffers& b,
+                cudaStream_t stream) {
+  GM_REQUIRE(edge_dim >= 1 && edge_dim <= kMaxIn1, "tc_enc_edge: edge_dim=%d outside [1,%d]", edge_dim, kMaxIn1);
+  GM_REQUIRE(edge_attr != nullptr || edge_dim == 4, "tc_enc_edge: on-the-fly edge features need edge_dim == 4");
+  if (g.max_edges <= 0) return GM_OK;
+  const size_t sm = smem_bytes(1);
+  int rc = tc_configure();
+  if (rc) return rc;
+  const int grid = min(ceil_div(g.max_edges, kTile), kNumSMs);
+  enc_edge_kernel<<<grid, NT, sm, stream>>>(m, edge_dim, pos, pos_stride, conn_r, edge_attr, eref, g, b);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("enc_edge_kernel");
+  return GM_OK;
+}
+
+int tc_pack_chunk(const float* w, int ld, int col0, void* chunk, cudaStream_t stream) {
+  pack_chunk_kernel<<<ceil_div(kH * (kH / 8), 128), 128, 0, stream>>>(w, ld, col0, (char*)chunk);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("pack_chunk_kernel");
+  return GM_OK;
+}
+
+int tc_selftest_gemm(const float* x, const void* chunk, float* out, int M, cudaStream_t stream) {
+  GM_REQUIRE(M > 0 && M % kTile == 0, "tc_selftest_gemm: M=%d must be a positive multiple of %d", M, kTile);
+  const size_t sm = smem_bytes(1);
+  int rc = tc_configure();
+  if (rc) return rc;
+  selftest_gemm_kernel<<<min(M / kTile, kNumSMs), NT, sm, stream>>>(x, chunk, out, M);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("selftest_gemm_kernel");
+  return GM_OK;
+}
+
+}  // namespace gm

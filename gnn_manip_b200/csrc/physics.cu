@@ -1,0 +1,191 @@
+// Rows A2 and A5 -- node/edge feature build and the Euler integrator / rollout bookkeeping.
+//
+// A2 replaces GraphBoundedMultimaterial(Control).compute_nodes (gnn_manip/utils/collate_utils.py:195-232),
+// get_nodes_vel (gnn_manip/utils/utils.py:27-40) and get_edges_displacement (utils.py:43-61).
+// A5 replaces get_position_from_prediction (gnn_manip/utils/rollout_utils.py:145-158), the state
+// bookkeeping of CMAESolver.cma_objective (gnn_manip/utils/traj_utils.py:119-152) and
+// compute_particles_tmatrix (traj_utils.py:167-194).
+//
+// All arithmetic is IEEE fp32 with the reference's operation order and *no* FMA contraction
+// (true division, sqrt.rn), so node features and the integrator are bit-identical to the CPU
+// reference; the edge norm uses the fused accumulation torch.norm performs on CPU.
+#include "common.cuh"
+#include "physics.cuh"
+
+namespace gm {
+
+namespace {
+
+__global__ void node_features_kernel(const float* __restrict__ obs, int k, int n, int D, PhysParams p,
+                                     float* __restrict__ nodes) {
+  const int F = p.node_dim;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)n * F) return;
+  const int node = (int)(idx / F), f = (int)(idx - (long long)node * F);
+  const int nvel = 3 * (k - 1);
+  const float* last = obs + ((size_t)(k - 1) * n + node) * D;
+  float out;
+  if (f < nvel) {
+    const int t = f / 3, d = f - 3 * t;
+    const float a = obs[((size_t)(t + 1) * n + node) * D + p.cart[d]];
+    const float b = obs[((size_t)t * n + node) * D + p.cart[d]];
+    out = __fdiv_rn(__fsub_rn(__fsub_rn(a, b), p.vel_mean[d]), p.vel_std[d]);
+  } else if (f < nvel + 6) {
+    const int b = f - nvel, d = b % 3;
+    const float x = last[p.cart[d]];
+    const float dist = b < 3 ? __fsub_rn(x, p.lower[d]) : __fsub_rn(p.upper[d], x);
+    const float q = __fdiv_rn(dist, p.conn_r);
+    out = fminf(fmaxf(q, -1.0f), 1.0f);
+    if (q != q) out = q;  // torch.clamp propagates NaN
+  } else if (f == nvel + 6) {
+    out = last[p.mat];
+  } else {
+    const int d = f - (nvel + 7);
+    out = __fdiv_rn(__fsub_rn(last[p.ctrl[d]], p.vel_mean[d]), p.vel_std[d]);
+  }
+  nodes[idx] = out;
+}
+
+__global__ void edge_features_kernel(const float* __restrict__ pos, int stride, const int* __restrict__ send,
+                                     const int* __restrict__ recv, const int* __restrict__ n_edges_dev,
+                                     int max_edges, float conn_r, float4* __restrict__ edge_attr) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int ne = n_edges_dev ? min(*n_edges_dev, max_edges) : max_edges;
+  if (e >= ne) return;
+  edge_attr[e] = edge_feature(pos, stride, send[e], recv[e], conn_r);
+}
+
+// Rigid ("cup") particle r of graph g at rollout step i: rotation about X by rot, Y shift by ty around
+// ty_init with y/z swapped and the offset taken as (ty_init - p) (traj_utils.py:167-194).
+__device__ __forceinline__ void rigid_target(const RolloutParams& rp, int g, int r, int step, float out[3]) {
+  if (rp.traj != nullptr) {
+    const float* t = rp.traj + (((size_t)g * rp.traj_steps + step) * rp.n_rigid + r) * 3;
+    out[0] = t[0]; out[1] = t[1]; out[2] = t[2];
+    return;
+  }
+  const double rot = rp.rot[(size_t)g * rp.traj_steps + step];
+  const double ty = rp.ty[(size_t)g * rp.traj_steps + step];
+  const float c = (float)cos(rot), s = (float)sin(rot);
+  const float t1 = (float)((double)rp.ty_init[1] + ty);   // torch.tensor(..., dtype=float32) of an f64 sum
+  const float* p0 = rp.rigid_init + (size_t)r * 3;
+  const float q0 = __fsub_rn(rp.ty_init[0], p0[0]);
+  const float q1 = __fsub_rn(rp.ty_init[1], p0[2]);
+  const float q2 = __fsub_rn(rp.ty_init[2], p0[1]);
+  const float w0 = __fadd_rn(q0, rp.ty_init[0]);
+  const float w1 = __fadd_rn(__fadd_rn(__fmul_rn(c, q1), __fmul_rn(-s, q2)), t1);
+  const float w2 = __fadd_rn(__fadd_rn(__fmul_rn(s, q1), __fmul_rn(c, q2)), rp.ty_init[2]);
+  out[0] = w0; out[1] = w2; out[2] = w1;
+}
+
+// Step (1) of the loop body: control columns of the rigid particles (traj_utils.py:126-135).
+__global__ void apply_control_kernel(float* __restrict__ obs, RolloutParams rp) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= rp.n_graphs * rp.n_rigid) return;
+  const int g = idx / rp.n_rigid, r = idx - g * rp.n_rigid;
+  const int step = *rp.step_dev;
+  const int node = g * rp.n_per_graph + rp.rigid_idx[r];
+  const int n = rp.n_graphs * rp.n_per_graph;
+  float* last = obs + ((size_t)(rp.k - 1) * n + node) * rp.D;
+  float tgt[3];
+  if (step < rp.traj_steps) {
+    rigid_target(rp, g, r, step, tgt);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      rp.rigid_tgt[(size_t)idx * 3 + d] = tgt[d];
+      last[rp.phys.ctrl[d]] = __fsub_rn(tgt[d], last[rp.phys.cart[d]]);
+    }
+  } else {  // reference quirk traj_utils.py:128-129: control := position, state left to the model
+#pragma unroll
+    for (int d = 0; d < 3; ++d) last[rp.phys.ctrl[d]] = last[rp.phys.cart[d]];
+  }
+}
+
+// Steps (3)+(4): semi-implicit Euler, window shift, rigid overwrite (rollout_utils.py:145-158,
+// traj_utils.py:146-152). One thread per node; each node's rows are private to its thread.
+__global__ void integrate_kernel(float* __restrict__ obs, const float* __restrict__ pred, RolloutParams rp,
+                                 float* __restrict__ next_pos_out) {
+  const int node = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = rp.n_graphs * rp.n_per_graph;
+  if (node >= n) return;
+  const int k = rp.k, D = rp.D;
+  const PhysParams& p = rp.phys;
+  float nxt[3];
+  {
+    const float* last = obs + ((size_t)(k - 1) * n + node) * D;
+    const float* prev = obs + ((size_t)(k - 2) * n + node) * D;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const float acc = __fadd_rn(__fmul_rn(pred[(size_t)node * 3 + d], p.acc_std[d]), p.acc_mean[d]);
+      const float lp = last[p.cart[d]];
+      const float vel = __fadd_rn(__fsub_rn(lp, prev[p.cart[d]]), acc);
+      nxt[d] = __fadd_rn(lp, vel);
+    }
+  }
+  if (next_pos_out) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) next_pos_out[(size_t)node * 3 + d] = nxt[d];
+  }
+  for (int t = 0; t + 1 < k; ++t) {
+    const float* src = obs + ((size_t)(t + 1) * n + node) * D;
+    float* dst = obs + ((size_t)t * n + node) * D;
+    for (int c = 0; c < D; ++c) dst[c] = src[c];
+  }
+  float* last = obs + ((size_t)(k - 1) * n + node) * D;
+  const int local = node % rp.n_per_graph;
+  const int rslot = rp.rigid_slot ? rp.rigid_slot[local] : -1;
+  const int step = *rp.step_dev;
+  if (rslot >= 0 && step < rp.traj_steps) {
+    const int g = node / rp.n_per_graph;
+    const float* tgt = rp.rigid_tgt + ((size_t)g * rp.n_rigid + rslot) * 3;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) last[p.cart[d]] = tgt[d];
+  } else {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) last[p.cart[d]] = nxt[d];
+  }
+}
+
+__global__ void bump_step_kernel(int* step_dev) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *step_dev += 1;
+}
+
+}  // namespace
+
+int node_features(const float* obs, int k, int n, int D, const PhysParams& p, float* nodes, cudaStream_t stream) {
+  GM_REQUIRE(k >= 2 && n > 0 && D > 0, "node_features: bad shape k=%d n=%d D=%d", k, n, D);
+  const long long total = (long long)n * p.node_dim;
+  node_features_kernel<<<ceil_div(total, 256), 256, 0, stream>>>(obs, k, n, D, p, nodes);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("node_features_kernel");
+  return GM_OK;
+}
+
+int edge_features(const float* pos, int stride, const int* send, const int* recv, const int* n_edges_dev,
+                  int max_edges, float conn_r, float* edge_attr, cudaStream_t stream) {
+  if (max_edges <= 0) return GM_OK;
+  edge_features_kernel<<<ceil_div(max_edges, 256), 256, 0, stream>>>(pos, stride, send, recv, n_edges_dev,
+                                                                    max_edges, conn_r, (float4*)edge_attr);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("edge_features_kernel");
+  return GM_OK;
+}
+
+int apply_control(float* obs, const RolloutParams& rp, cudaStream_t stream) {
+  const int total = rp.n_graphs * rp.n_rigid;
+  if (total <= 0) return GM_OK;
+  apply_control_kernel<<<ceil_div(total, 128), 128, 0, stream>>>(obs, rp);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("apply_control_kernel");
+  return GM_OK;
+}
+
+int integrate(float* obs, const float* pred, const RolloutParams& rp, float* next_pos_out, cudaStream_t stream) {
+  const int n = rp.n_graphs * rp.n_per_graph;
+  integrate_kernel<<<ceil_div(n, 128), 128, 0, stream>>>(obs, pred, rp, next_pos_out);
+  bump_step_kernel<<<1, 32, 0, stream>>>(rp.step_dev);
+  GM_LAUNCHED(2);
+  GM_LAUNCH_CHECK("integrate_kernel");
+  return GM_OK;
+}
+
+}  // namespace gm

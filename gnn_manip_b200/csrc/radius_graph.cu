@@ -1,0 +1,422 @@
+// Row A1 -- capped radius graph as a cell-list spatial hash with a warp-cooperative neighbour scan.
+//
+// Replaces gnn_manip/utils/utils.py:64-93 (get_connectivity: sklearn KDTree.query_radius sorted by
+// distance, first max_neighbours kept per query).  Truncation rule reproduced exactly:
+//   for every query i (= sender): all j with d2(i,j) <= r*r (self included), ordered by ascending
+//   distance (ties: ascending j -- undefined in the reference), first K kept.
+// d2 is evaluated like scikit-learn's KDTree64: float32 inputs widened to float64,
+// d2 = ((dx*dx) + dy*dy) + dz*dz with round-to-nearest and no FMA contraction
+// (sklearn/metrics/_dist_metrics.pxd.tp:39-49, neighbors/_binary_tree.pxi.tp:1952-1967).
+//
+// Outputs (all int32, device):
+//   nbr [n, K], cnt [n]     sender-major neighbour table == the reference edge list when flattened
+//   edge_ptr [n+1]          exclusive scan of cnt: reference edge id of (i, s) is edge_ptr[i] + s
+//   recv_ptr [n+1]          receiver CSR offsets
+//   esend/erecv/eref [n*K]  edges sorted by (receiver, sender): sender, receiver, reference edge id
+//   n_edges (device scalar) = edge_ptr[n]
+// The receiver-major order is what the message-passing kernels consume: a receiver's incoming edges are
+// contiguous, so the scatter_add of graph_networks.py:75-85 becomes a deterministic segmented sum that
+// visits the edges of each receiver in ascending reference edge id (the CPU order of index_add_).
+#include "common.cuh"
+#include "scan.cuh"
+#include "radius_graph.cuh"
+
+namespace gm {
+
+namespace {
+
+struct GridParams {
+  double lo[3];
+  double cs;        // cell edge (>= r * (1 + 1e-6))
+  int dim[3];
+  int cells_per_graph;
+};
+
+__device__ __forceinline__ unsigned f2ord(float f) {
+  unsigned u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned u) {
+  return __uint_as_float((u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u);
+}
+
+__global__ void bbox_init_kernel(unsigned* bbox) {
+  if (threadIdx.x < 3) bbox[threadIdx.x] = 0xFFFFFFFFu;          // min
+  else if (threadIdx.x < 6) bbox[threadIdx.x] = 0u;              // max
+}
+
+__global__ void bbox_kernel(const float* __restrict__ pos, int stride, int n, unsigned* __restrict__ bbox) {
+  unsigned mn[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, mx[3] = {0u, 0u, 0u};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      unsigned o = f2ord(pos[(size_t)i * stride + d]);
+      mn[d] = min(mn[d], o);
+      mx[d] = max(mx[d], o);
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[d] = min(mn[d], __shfl_xor_sync(0xffffffffu, mn[d], o));
+      mx[d] = max(mx[d], __shfl_xor_sync(0xffffffffu, mx[d], o));
+    }
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      atomicMin(&bbox[d], mn[d]);
+      atomicMax(&bbox[3 + d], mx[d]);
+    }
+  }
+}
+
+// One thread: choose the cell edge so that (cells per graph) * n_graphs fits the cell budget.
+__global__ void grid_setup_kernel(const unsigned* __restrict__ bbox, double r, int n_graphs, int max_cells,
+                                  GridParams* __restrict__ gp) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double lo[3], ext[3];
+  for (int d = 0; d < 3; ++d) {
+    lo[d] = (double)ord2f(bbox[d]);
+    double hi = (double)ord2f(bbox[3 + d]);
+    ext[d] = hi - lo[d];
+    if (!(ext[d] >= 0.0)) ext[d] = 0.0;  // empty / NaN input
+  }
+  double cs = r * (1.0 + 1e-6);
+  if (!(cs > 0.0)) cs = 1.0;
+  int dim[3];
+  const double budget = (double)max_cells / (double)(n_graphs > 0 ? n_graphs : 1);
+  for (int it = 0; it < 200; ++it) {
+    double prod = 1.0;
+    for (int d = 0; d < 3; ++d) {
+      double c = floor(ext[d] / cs) + 1.0;
+      if (c > 2.0e6) c = 2.0e6;
+      dim[d] = (int)c;
+      prod *= c;
+    }
+    if (prod <= budget) break;
+    cs *= 1.26;
+  }
+  for (int d = 0; d < 3; ++d) {
+    gp->lo[d] = lo[d];
+    gp->dim[d] = dim[d];
+  }
+  gp->cs = cs;
+  gp->cells_per_graph = dim[0] * dim[1] * dim[2];
+}
+
+__device__ __forceinline__ void cell_coords(const GridParams& gp, float x, float y, float z, int c[3]) {
+  const float p[3] = {x, y, z};
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    // fp64 keeps floor((p - lo)/cs) monotone, so |dx| <= r < cs never skips a cell
+    int v = (int)floor(((double)p[d] - gp.lo[d]) / gp.cs);
+    c[d] = min(max(v, 0), gp.dim[d] - 1);
+  }
+}
+
+__global__ void cell_count_kernel(const float* __restrict__ pos, int stride, int n, int n_per_graph,
+                                  const GridParams* __restrict__ gpp, int* __restrict__ cell_of,
+                                  int* __restrict__ cell_cnt) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const GridParams gp = *gpp;
+  const float* p = pos + (size_t)i * stride;
+  int c[3];
+  cell_coords(gp, p[0], p[1], p[2], c);
+  int g = i / n_per_graph;
+  int cell = g * gp.cells_per_graph + (c[2] * gp.dim[1] + c[1]) * gp.dim[0] + c[0];
+  cell_of[i] = cell;
+  atomicAdd(&cell_cnt[cell], 1);
+}
+
+// sorted[slot] = (x, y, z, node id); consumes cell_cnt back to zero.
+__global__ void cell_fill_kernel(const float* __restrict__ pos, int stride, int n,
+                                 const int* __restrict__ cell_of, const int* __restrict__ cell_start,
+                                 int* __restrict__ cell_cnt, float4* __restrict__ sorted) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int cell = cell_of[i];
+  int slot = cell_start[cell] + atomicSub(&cell_cnt[cell], 1) - 1;
+  const float* p = pos + (size_t)i * stride;
+  sorted[slot] = make_float4(p[0], p[1], p[2], __int_as_float(i));
+}
+
+constexpr int kNbrWarps = 8;      // warps (queries) per block
+constexpr int kNbrBuf = 192;      // in-radius candidate buffer per warp
+constexpr int kMaxK = 64;
+
+__device__ __forceinline__ bool key_less(double da, int ja, double db, int jb) {
+  return da < db || (da == db && ja < jb);
+}
+
+// Keep the `keep` smallest (d2, j) keys of buf[0..cnt) in sorted order at the front of buf.
+__device__ __forceinline__ void warp_select_smallest(double* bd, int* bj, double* td, int* tj, int cnt, int keep,
+                                                     int lane) {
+  for (int e = lane; e < cnt; e += 32) {
+    const double de = bd[e];
+    const int je = bj[e];
+    int rank = 0;
+    for (int o = 0; o < cnt; ++o) rank += key_less(bd[o], bj[o], de, je) ? 1 : 0;
+    if (rank < keep) {
+      td[rank] = de;
+      tj[rank] = je;
+    }
+  }
+  __syncwarp();
+  const int m = cnt < keep ? cnt : keep;
+  for (int e = lane; e < m; e += 32) {
+    bd[e] = td[e];
+    bj[e] = tj[e];
+  }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(kNbrWarps * 32)
+neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
+                 const GridParams* __restrict__ gpp, int n, int n_per_graph, double r2, int K,
+                 int* __restrict__ nbr, int* __restrict__ cnt_out, int* __restrict__ indeg) {
+  __shared__ double s_bd[kNbrWarps][kNbrBuf];
+  __shared__ int s_bj[kNbrWarps][kNbrBuf];
+  __shared__ double s_td[kNbrWarps][kMaxK];
+  __shared__ int s_tj[kNbrWarps][kMaxK];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int q = blockIdx.x * kNbrWarps + w;  // query in cell-sorted order (neighbouring warps share cells)
+  if (q >= n) return;
+  const GridParams gp = *gpp;
+  double* bd = s_bd[w];
+  int* bj = s_bj[w];
+  double* td = s_td[w];
+  int* tj = s_tj[w];
+
+  const float4 me = sorted[q];
+  const int qi = __float_as_int(me.w);
+  const double px = (double)me.x, py = (double)me.y, pz = (double)me.z;
+  int c[3];
+  cell_coords(gp, me.x, me.y, me.z, c);
+  const int gbase = (qi / n_per_graph) * gp.cells_per_graph;
+
+  int count = 0;
+  for (int dz = -1; dz <= 1; ++dz) {
+    const int z = c[2] + dz;
+    if (z < 0 || z >= gp.dim[2]) continue;
+    for (int dy = -1; dy <= 1; ++dy) {
+      const int y = c[1] + dy;
+      if (y < 0 || y >= gp.dim[1]) continue;
+      const int x0 = max(c[0] - 1, 0), x1 = min(c[0] + 1, gp.dim[0] - 1);
+      const int row = gbase + (z * gp.dim[1] + y) * gp.dim[0];
+      const int beg = cell_start[row + x0], end = cell_start[row + x1 + 1];
+      for (int s0 = beg; s0 < end; s0 += 32) {
+        const int s = s0 + lane;
+        bool in = false;
+        double d2 = 0.0;
+        int j = -1;
+        if (s < end) {
+          const float4 o = sorted[s];
+          const double dx = px - (double)o.x, dyy = py - (double)o.y, dzz = pz - (double)o.z;
+          d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dyy, dyy)), __dmul_rn(dzz, dzz));
+          in = d2 <= r2;
+          j = __float_as_int(o.w);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, in);
+        if (in) {
+          const int at = count + __popc(m & ((1u << lane) - 1u));
+          bd[at] = d2;
+          bj[at] = j;
+        }
+        count += __popc(m);
+        __syncwarp();
+        if (count + 32 > kNbrBuf) {  // keep only the K best so far, then continue scanning
+          warp_select_smallest(bd, bj, td, tj, count, K, lane);
+          count = min(count, K);
+        }
+      }
+    }
+  }
+  warp_select_smallest(bd, bj, td, tj, count, K, lane);
+  const int kept = min(count, K);
+  for (int e = lane; e < K; e += 32) {
+    const int j = e < kept ? bj[e] : -1;
+    nbr[(size_t)qi * K + e] = j;
+    if (j >= 0) atomicAdd(&indeg[j], 1);
+  }
+  if (lane == 0) cnt_out[qi] = kept;
+}
+
+// ---- receiver CSR over "edge slots" (slot -> receiver, -1 = empty slot) ----
+__global__ void indeg_count_kernel(const int* __restrict__ recv_of_slot, long long n_slots,
+                                   const int* __restrict__ n_valid_dev, int* __restrict__ indeg) {
+  long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_slots) return;
+  if (n_valid_dev && s >= *n_valid_dev) return;
+  int j = recv_of_slot[s];
+  if (j >= 0) atomicAdd(&indeg[j], 1);
+}
+
+__global__ void recv_fill_kernel(const int* __restrict__ recv_of_slot, long long n_slots,
+                                 const int* __restrict__ n_valid_dev, const int* __restrict__ recv_ptr,
+                                 int* __restrict__ fill, int* __restrict__ keys) {
+  long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_slots) return;
+  if (n_valid_dev && s >= *n_valid_dev) return;
+  int j = recv_of_slot[s];
+  if (j < 0) return;
+  int at = recv_ptr[j] + atomicAdd(&fill[j], 1);
+  keys[at] = (int)s;
+}
+
+// One thread per receiver: sort its slot keys ascending (== ascending sender, == reference edge order),
+// then emit sender / receiver / reference edge id for every sorted edge.
+__global__ void recv_sort_emit_kernel(const int* __restrict__ recv_ptr, int n, int* __restrict__ keys,
+                                      int K /*>0: slot = sender*K + s; 0: slot = edge id*/,
+                                      const int* __restrict__ edge_ptr, const int* __restrict__ send_of_slot,
+                                      int* __restrict__ esend, int* __restrict__ erecv, int* __restrict__ eref) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const int b = recv_ptr[j], e = recv_ptr[j + 1];
+  const int len = e - b;
+  constexpr int kLocal = 48;
+  if (len <= kLocal) {
+    int buf[kLocal];
+#pragma unroll 1
+    for (int t = 0; t < len; ++t) buf[t] = keys[b + t];
+#pragma unroll 1
+    for (int t = 1; t < len; ++t) {
+      int v = buf[t], u = t - 1;
+      while (u >= 0 && buf[u] > v) {
+        buf[u + 1] = buf[u];
+        --u;
+      }
+      buf[u + 1] = v;
+    }
+#pragma unroll 1
+    for (int t = 0; t < len; ++t) keys[b + t] = buf[t];
+  } else {
+    for (int t = b + 1; t < e; ++t) {
+      int v = keys[t], u = t - 1;
+      while (u >= b && keys[u] > v) {
+        keys[u + 1] = keys[u];
+        --u;
+      }
+      keys[u + 1] = v;
+    }
+  }
+  for (int t = b; t < e; ++t) {
+    const int slot = keys[t];
+    int snd, ref;
+    if (K > 0) {
+      snd = slot / K;
+      ref = edge_ptr[snd] + (slot - snd * K);
+    } else {
+      snd = send_of_slot[slot];
+      ref = slot;
+    }
+    esend[t] = snd;
+    erecv[t] = j;
+    eref[t] = ref;
+  }
+}
+
+__global__ void copy_last_kernel(const int* __restrict__ ptr, int n, int* __restrict__ out) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *out = ptr[n];
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+size_t radius_graph_workspace_bytes(int n_total, int n_graphs, int K) {
+  Arena a(nullptr, 0);
+  RadiusGraphWs ws;
+  radius_graph_carve(a, n_total, n_graphs, K, ws);
+  return a.off + 256;
+}
+
+int radius_graph_max_cells(int n_total) {
+  long long c = 4LL * n_total;
+  if (c < 4096) c = 4096;
+  if (c > (1LL << 22)) c = 1LL << 22;
+  return (int)c;
+}
+
+void radius_graph_carve(Arena& a, int n_total, int /*n_graphs*/, int K, RadiusGraphWs& ws) {
+  ws.max_cells = radius_graph_max_cells(n_total);
+  ws.bbox = a.take<unsigned>(8);
+  ws.grid = a.take<char>(sizeof(GridParams));
+  ws.cell_of = a.take<int>(n_total);
+  ws.cell_cnt = a.take<int>((size_t)ws.max_cells + 1);
+  ws.cell_start = a.take<int>((size_t)ws.max_cells + 2);
+  ws.sorted = a.take<float4>(n_total);
+  ws.indeg = a.take<int>((size_t)n_total + 1);   // indeg and fill are contiguous: one memset
+  ws.fill = a.take<int>((size_t)n_total + 1);
+  ws.keys = a.take<int>((size_t)n_total * K);
+  size_t scan_n = (size_t)ws.max_cells + 1 > (size_t)n_total + 1 ? (size_t)ws.max_cells + 1 : (size_t)n_total + 1;
+  ws.scan_ws = a.take<int>(scan_workspace_ints((long long)scan_n) + 8);
+}
+
+int build_recv_csr(const int* recv_of_slot, long long n_slots, const int* n_valid_dev, int n_nodes, int K,
+                   const int* edge_ptr, const int* send_of_slot, int* indeg, int* fill, int* keys, int* scan_ws,
+                   bool indeg_ready, int* recv_ptr, int* esend, int* erecv, int* eref, cudaStream_t stream) {
+  const int T = 256;
+  if (!indeg_ready) {
+    GM_CUDA(cudaMemsetAsync(indeg, 0, sizeof(int) * ((size_t)n_nodes + 1), stream));
+    if (n_slots > 0) {
+      indeg_count_kernel<<<ceil_div(n_slots, T), T, 0, stream>>>(recv_of_slot, n_slots, n_valid_dev, indeg);
+      GM_LAUNCHED(1);
+    }
+  }
+  GM_CUDA(cudaMemsetAsync(fill, 0, sizeof(int) * ((size_t)n_nodes + 1), stream));
+  int rc = exclusive_scan_i32(indeg, recv_ptr, n_nodes, scan_ws, stream);
+  if (rc) return rc;
+  if (n_slots > 0) {
+    recv_fill_kernel<<<ceil_div(n_slots, T), T, 0, stream>>>(recv_of_slot, n_slots, n_valid_dev, recv_ptr, fill, keys);
+    GM_LAUNCHED(1);
+  }
+  if (n_nodes > 0) {
+    recv_sort_emit_kernel<<<ceil_div(n_nodes, 128), 128, 0, stream>>>(recv_ptr, n_nodes, keys, K, edge_ptr,
+                                                                     send_of_slot, esend, erecv, eref);
+    GM_LAUNCHED(1);
+  }
+  GM_LAUNCH_CHECK("build_recv_csr");
+  return GM_OK;
+}
+
+int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs, double r, int K, int* nbr,
+                 int* cnt, int* edge_ptr, int* recv_ptr, int* esend, int* erecv, int* eref, int* n_edges,
+                 const RadiusGraphWs& ws, cudaStream_t stream) {
+  const long long n_ll = (long long)n_per_graph * n_graphs;
+  GM_REQUIRE(n_per_graph > 0 && n_graphs > 0, "radius_graph: empty input (n_per_graph=%d n_graphs=%d)",
+             n_per_graph, n_graphs);
+  GM_REQUIRE(K >= 1 && K <= kMaxK, "radius_graph: max_neighbours=%d outside [1,%d]", K, kMaxK);
+  GM_REQUIRE(n_ll * K < (1LL << 31), "radius_graph: n*K=%lld overflows int32 slots", n_ll * K);
+  GM_REQUIRE(r > 0.0, "radius_graph: conn_r must be positive");
+  const int n = (int)n_ll;
+  const int T = 256;
+  GridParams* gp = reinterpret_cast<GridParams*>(ws.grid);
+
+  bbox_init_kernel<<<1, 32, 0, stream>>>(ws.bbox);
+  bbox_kernel<<<min(ceil_div(n, T), 4 * kNumSMs), T, 0, stream>>>(pos, pos_stride, n, ws.bbox);
+  grid_setup_kernel<<<1, 32, 0, stream>>>(ws.bbox, r, n_graphs, ws.max_cells, gp);
+  GM_CUDA(cudaMemsetAsync(ws.cell_cnt, 0, sizeof(int) * ((size_t)ws.max_cells + 1), stream));
+  GM_CUDA(cudaMemsetAsync(ws.indeg, 0, sizeof(int) * ((size_t)n + 1), stream));
+  cell_count_kernel<<<ceil_div(n, T), T, 0, stream>>>(pos, pos_stride, n, n_per_graph, gp, ws.cell_of, ws.cell_cnt);
+  int rc = exclusive_scan_i32(ws.cell_cnt, ws.cell_start, ws.max_cells, ws.scan_ws, stream);
+  if (rc) return rc;
+  cell_fill_kernel<<<ceil_div(n, T), T, 0, stream>>>(pos, pos_stride, n, ws.cell_of, ws.cell_start, ws.cell_cnt,
+                                                     ws.sorted);
+  neighbour_kernel<<<ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream>>>(
+      ws.sorted, ws.cell_start, gp, n, n_per_graph, r * r, K, nbr, cnt, ws.indeg);
+  GM_LAUNCHED(6);
+  GM_LAUNCH_CHECK("radius_graph kernels");
+  rc = exclusive_scan_i32(cnt, edge_ptr, n, ws.scan_ws, stream);
+  if (rc) return rc;
+  rc = build_recv_csr(nbr, (long long)n * K, nullptr, n, K, edge_ptr, nullptr, ws.indeg, ws.fill, ws.keys,
+                      ws.scan_ws, /*indeg_ready=*/true, recv_ptr, esend, erecv, eref, stream);
+  if (rc) return rc;
+  copy_last_kernel<<<1, 32, 0, stream>>>(edge_ptr, n, n_edges);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("radius_graph tail");
+  return GM_OK;
+}
+
+}  // namespace gm

@@ -1,0 +1,197 @@
+/* gnn_manip_b200 -- C ABI of the B200-native gnn-manip rollout hot path.
+ *
+ * Drop-in boundary for the Encode-Process-Decode GraphNet rollout of dblanm/gnn-manip.  The reference has no
+ * FFI of its own (it is pure Python); each entry point below names the reference function it replaces
+ * (paths relative to the reference checkout) and is what a ctypes / torch-extension binding on the
+ * reference side calls.
+ *
+ * Conventions
+ *   - every pointer is DEVICE memory unless the name ends in _host; tensors are dense, row-major, fp32 / int32
+ *   - the library never allocates device memory: scratch is a caller-provided workspace whose size comes
+ *     from the matching *_workspace_bytes() query
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); nothing synchronises the host
+ *   - return value: 0 = ok, otherwise a gm_status code; gm_last_error() gives the message (thread-local)
+ *   - no exceptions cross the ABI
+ *   - graph sizes that are only known on the device (edge counts) stay on the device: kernels are launched
+ *     for the static upper bound max_edges = n_nodes * max_neighbours and read the live count themselves,
+ *     which is what makes a whole rollout step capturable in a CUDA graph
+ */
+#ifndef GNN_MANIP_B200_H_
+#define GNN_MANIP_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum gm_status {
+  GM_STATUS_OK = 0,
+  GM_STATUS_INVALID = 1,
+  GM_STATUS_WORKSPACE = 2,
+  GM_STATUS_CUDA = 3,
+  GM_STATUS_UNSUPPORTED = 4
+};
+
+/* which kernels run the MLPs */
+enum gm_impl {
+  GM_IMPL_AUTO = 0,   /* tcgen05 path when the model is hidden=128 / num_layers=2 / LayerNorm, else fp32 CUDA cores */
+  GM_IMPL_SIMT = 1,   /* generic fp32 CUDA-core kernels (any widths) */
+  GM_IMPL_TC = 2      /* tcgen05 / TMEM kernels (error if the model shape is not covered) */
+};
+
+int gm_version(void);
+const char* gm_last_error(void);
+
+/* Dataset constants (schema: gnn_manip/utils/coffee_dataset.py:18-43, read_metadata). Host struct, by pointer. */
+typedef struct gm_phys {
+  int32_t cartesian_idx[3];
+  int32_t material_idx;
+  int32_t control_idx[3];     /* ignored when use_control == 0 */
+  int32_t use_control;        /* GraphBoundedMultimaterialControl vs GraphBoundedMultimaterial */
+  float velocity_mean[3], velocity_std[3];
+  float acceleration_mean[3], acceleration_std[3];
+  float lower_bounds[3], upper_bounds[3];
+  double conn_r;
+} gm_phys;
+
+/* ---------------------------------------------------------------------------------------------------------
+ * A1  radius graph -- replaces get_connectivity (gnn_manip/utils/utils.py:64-93; sklearn KDTree.query_radius,
+ *     sort_results=True, first max_neighbours kept per query node, self-loop included).
+ *
+ * pos: first coordinate of node 0; node i is at pos + i*pos_stride (x,y,z contiguous), so the last frame of an
+ *      observation tensor obs[k,N,D] can be passed in place (pos = obs_last + cartesian_idx[0], stride = D).
+ * n_graphs independent graphs of n_per_graph nodes each are built in one call; node ids are global
+ *      (graph g owns [g*n_per_graph, (g+1)*n_per_graph)), the offset rule of collate_utils.py:75-76.
+ * Outputs (int32):
+ *   nbr [n, K] / cnt [n]   neighbour table; flattened row-major over valid entries it IS the reference edge
+ *                          list: senders = repeat(i, cnt[i]), receivers = nbr[i, :cnt[i]]
+ *   edge_ptr [n+1]         exclusive scan of cnt (reference edge id of (i, s) = edge_ptr[i] + s)
+ *   recv_ptr [n+1], esend / erecv / eref [n*K]   the same edges sorted by (receiver, sender): CSR offsets,
+ *                          sender, receiver and reference edge id of every sorted edge
+ *   n_edges [1]            number of edges
+ * --------------------------------------------------------------------------------------------------------- */
+size_t gm_radius_graph_workspace_bytes(int32_t n_per_graph, int32_t n_graphs, int32_t max_neighbours);
+int gm_radius_graph(const float* pos, int32_t pos_stride, int32_t n_per_graph, int32_t n_graphs, double conn_r,
+                    int32_t max_neighbours, int32_t* nbr, int32_t* cnt, int32_t* edge_ptr, int32_t* recv_ptr,
+                    int32_t* esend, int32_t* erecv, int32_t* eref, int32_t* n_edges, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
+/* Expand (nbr, cnt, edge_ptr) into the reference's int64 edge_index [2, n_edges_host] (senders row 0,
+ * receivers row 1) -- the compatibility surface of process_collate (collate_utils.py:68-87). */
+int gm_edge_index_i64(const int32_t* nbr, const int32_t* cnt, const int32_t* edge_ptr, int32_t n_nodes,
+                      int32_t max_neighbours, int64_t n_edges_host, int64_t* edge_index, void* stream);
+
+/* Receiver CSR of an explicit edge list (any graph): stable sort of edges by receiver.
+ * senders/receivers int32 [n_edges]; outputs as in gm_radius_graph. */
+size_t gm_recv_csr_workspace_bytes(int32_t n_nodes, int64_t n_edges);
+int gm_recv_csr(const int32_t* senders, const int32_t* receivers, int64_t n_edges, int32_t n_nodes,
+                int32_t* recv_ptr, int32_t* esend, int32_t* erecv, int32_t* eref, void* workspace,
+                size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * A2  features -- replaces GraphBoundedMultimaterial(Control).compute_nodes (collate_utils.py:195-232) with
+ *     get_nodes_vel (utils.py:27-40), and get_edges_displacement (utils.py:43-61).
+ * obs [k, n, D]; nodes [n, 3(k-1)+6+1(+3)]; edge_attr [n_edges, 4] in the order of the given senders/receivers.
+ * n_edges_dev may be NULL (then max_edges edges are processed).
+ * --------------------------------------------------------------------------------------------------------- */
+int32_t gm_node_dim(int32_t k, int32_t use_control);
+int gm_node_features(const float* obs, int32_t k, int32_t n, int32_t D, const gm_phys* phys_host, float* nodes,
+                     void* stream);
+int gm_edge_features(const float* pos, int32_t pos_stride, const int32_t* senders, const int32_t* receivers,
+                     const int32_t* n_edges_dev, int32_t max_edges, double conn_r, float* edge_attr, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * A3/A4  model -- replaces EncProcDecGNN (gnn_manip/models/epd_gnn.py:11-105) and the blocks it is made of
+ *        (deps/torch-graphnet/torch_graphnet/graph_networks.py:19-137, utils/gn_utils.py:7-64).
+ *
+ * flat_params: every *unique* parameter of the state dict, fp32, concatenated in this order
+ *   encoder.phi_edge, encoder.phi_node, processor.0.phi_edge, processor.0.phi_node, ..., decoder
+ *   and inside each Sequential: Linear weights [out,in] then bias, layer by layer, then LayerNorm weight, bias.
+ * blob: device memory that receives the packed weights (size from gm_model_blob_bytes); must outlive the model.
+ * --------------------------------------------------------------------------------------------------------- */
+typedef struct gm_model gm_model;
+size_t gm_model_num_params(int32_t node_dim, int32_t edge_dim, int32_t out_dim, int32_t hidden, int32_t num_layers,
+                           int32_t m_steps);
+size_t gm_model_blob_bytes(int32_t node_dim, int32_t edge_dim, int32_t out_dim, int32_t hidden, int32_t num_layers,
+                           int32_t m_steps);
+int gm_model_create(gm_model** model, const float* flat_params, size_t n_params, int32_t node_dim, int32_t edge_dim,
+                    int32_t out_dim, int32_t hidden, int32_t num_layers, int32_t m_steps, void* blob,
+                    size_t blob_bytes, void* stream);
+void gm_model_destroy(gm_model* model);
+int gm_model_supports_tc(const gm_model* model);
+
+/* EncProcDecGNN.forward(nodes, edge_attr, edge_index) -> pred [n_nodes, out_dim] (epd_gnn.py:86-98).
+ * The graph is given in receiver-major form (gm_radius_graph / gm_recv_csr outputs).
+ * edge_attr: explicit edge features [n_edges, edge_dim] indexed by REFERENCE edge id (eref maps sorted edges to
+ *            them), or NULL to build the displacement features on the fly from pos (edge_dim must be 4). */
+size_t gm_forward_workspace_bytes(const gm_model* model, int32_t n_nodes, int32_t max_edges, int32_t impl);
+int gm_model_forward(const gm_model* model, int32_t impl, const float* nodes, const float* edge_attr,
+                     const float* pos, int32_t pos_stride, double conn_r, int32_t n_nodes, int32_t max_edges,
+                     const int32_t* n_edges_dev, const int32_t* recv_ptr, const int32_t* esend,
+                     const int32_t* erecv, const int32_t* eref, float* pred, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* Block-level entry points (any widths; fp32 CUDA cores) behind EdgeModel / NodeModel / GraphIndependent:
+ * out[m] = MLP(concat_s src[s][idx[s] ? idx[s][m] : m]) with ReLU between layers, optional LayerNorm(eps 1e-5).
+ * weights_t[l]: TRANSPOSED Linear weight [in_l, out_l]; all arrays of pointers are HOST arrays of device pointers. */
+int gm_mlp_forward(int32_t n_layers, const float* const* weights_t_host, const float* const* biases_host,
+                   const int32_t* dims_host /* n_layers+1 */, const float* ln_weight, const float* ln_bias,
+                   int32_t n_src, const float* const* src_host, const int32_t* const* idx_host,
+                   const int32_t* widths_host, int64_t n_rows, float* out, void* stream);
+/* scatter_sum (gn_utils.py:60-64) as a deterministic receiver-sorted segmented sum:
+ * agg[n] = sum_{t in [recv_ptr[n], recv_ptr[n+1])} src[eref[t]] in ascending t. */
+int gm_segment_sum(const float* src, int32_t width, const int32_t* recv_ptr, const int32_t* eref, int32_t n_nodes,
+                   float* agg, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * A5  integrator + rollout loop -- replaces get_position_from_prediction (gnn_manip/utils/rollout_utils.py:145-158)
+ *     and the loop body of CMAESolver.cma_objective (gnn_manip/utils/traj_utils.py:119-152) == compute_rollout
+ *     (rollout_utils.py:38-65), including compute_particles_tmatrix (traj_utils.py:167-194).
+ * --------------------------------------------------------------------------------------------------------- */
+/* next_pos [n,3] = pos[-1] + ((pos[-1] - pos[-2]) + (pred*acc_std + acc_mean)); obs is not modified. */
+int gm_next_position(const float* obs, int32_t k, int32_t n, int32_t D, const gm_phys* phys_host, const float* pred,
+                     float* next_pos, void* stream);
+
+typedef struct gm_rollout gm_rollout;
+typedef struct gm_rollout_desc {
+  const gm_model* model;
+  int32_t impl;               /* gm_impl */
+  gm_phys phys;
+  int32_t k, D;               /* obs is [k, n_graphs*n_per_graph, D] */
+  int32_t n_per_graph, n_graphs;
+  int32_t max_neighbours;
+  int32_t n_rigid;            /* rigid ("cup") particles per graph */
+  const int32_t* rigid_idx;   /* [n_rigid] local node ids (device) */
+  int32_t traj_steps;         /* rollout steps covered by the control trajectory */
+  const float* traj;          /* optional [n_graphs, traj_steps, n_rigid, 3] rigid positions per step, or NULL ... */
+  const double* rot;          /* ... then rot/ty [n_graphs, traj_steps] (radians / metres) drive compute_particles_tmatrix */
+  const double* ty;
+  const float* rigid_init;    /* [n_rigid, 3] rigid particle positions of the initial state (used with rot/ty) */
+  float ty_init[3];
+  float* obs;                 /* state, advanced in place */
+  float* pred;                /* optional [n, out_dim]: last normalised acceleration */
+  int32_t use_cuda_graph;     /* capture one step and replay it */
+} gm_rollout_desc;
+
+size_t gm_rollout_workspace_bytes(const gm_rollout_desc* desc_host);
+int gm_rollout_create(gm_rollout** plan, const gm_rollout_desc* desc_host, void* workspace, size_t workspace_bytes,
+                      void* stream);
+/* run `steps` rollout steps starting at the plan's current step index (reset with gm_rollout_reset). */
+int gm_rollout_run(gm_rollout* plan, int32_t steps, void* stream);
+int gm_rollout_reset(gm_rollout* plan, int32_t step, void* stream);
+/* device pointers into the plan's workspace holding the graph of the most recent step (for parity tests) */
+int gm_rollout_graph(const gm_rollout* plan, const int32_t** nbr, const int32_t** cnt, const int32_t** edge_ptr,
+                     const int32_t** n_edges, const float** nodes);
+int64_t gm_rollout_kernel_launches_per_step(const gm_rollout* plan);
+void gm_rollout_destroy(gm_rollout* plan);
+
+/* tcgen05 operand-path self test: out[M,128] = x[M,128] @ w[128,128]^T (bf16x3), M % 128 == 0.
+ * chunk: 64 KB device scratch for the packed weight. */
+int gm_selftest_gemm(const float* x, const float* w, void* chunk, float* out, int32_t M, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNN_MANIP_B200_H_ */
