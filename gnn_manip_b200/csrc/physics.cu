@@ -134,11 +134,15 @@ __global__ void integrate_kernel(float* __restrict__ obs, const float* __restric
   const int local = node % rp.n_per_graph;
   const int rslot = rp.rigid_slot ? rp.rigid_slot[local] : -1;
   const int step = *rp.step_dev;
-  if (rslot >= 0 && step < rp.traj_steps) {
-    const int g = node / rp.n_per_graph;
-    const float* tgt = rp.rigid_tgt + ((size_t)g * rp.n_rigid + rslot) * 3;
+  if (rslot >= 0) {
+    // traj_utils.py:149-152: the whole pre-shift rigid row is written back; its position columns are the control
+    // target while the trajectory lasts and the *old* position afterwards (rigid particles then stay frozen).
+    if (step < rp.traj_steps) {
+      const int g = node / rp.n_per_graph;
+      const float* tgt = rp.rigid_tgt + ((size_t)g * rp.n_rigid + rslot) * 3;
 #pragma unroll
-    for (int d = 0; d < 3; ++d) last[p.cart[d]] = tgt[d];
+      for (int d = 0; d < 3; ++d) last[p.cart[d]] = tgt[d];
+    }
   } else {
 #pragma unroll
     for (int d = 0; d < 3; ++d) last[p.cart[d]] = nxt[d];

@@ -43,6 +43,9 @@ enum gm_impl {
 
 int gm_version(void);
 const char* gm_last_error(void);
+/* kernels of this library launched so far by the calling thread (launch-site counter; a replayed CUDA graph
+ * counts gm_rollout_kernel_launches_per_step() per step instead) */
+long long gm_launch_count(void);
 
 /* Dataset constants (schema: gnn_manip/utils/coffee_dataset.py:18-43, read_metadata). Host struct, by pointer. */
 typedef struct gm_phys {
