@@ -65,6 +65,9 @@ SIGNATURES = {
     "gm_forward_workspace_bytes": (c_size_t, [c_void_p, c_int32, c_int32, c_int32]),
     "gm_model_forward": (ctypes.c_int, [c_void_p, c_int32, c_void_p, c_void_p, c_void_p, c_int32, c_double, c_int32,
                                         c_int32] + [c_void_p] * 7 + [c_size_t, c_void_p]),
+    "gm_model_forward_profile": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_double, c_int32,
+                                                c_int32] + [c_void_p] * 7 + [c_size_t, c_void_p, POINTER(c_float),
+                                                                             POINTER(c_int32)]),
     "gm_mlp_forward": (ctypes.c_int, [c_int32, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_int32), c_void_p,
                                       c_void_p, c_int32, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_int32),
                                       c_int64, c_void_p, c_void_p]),

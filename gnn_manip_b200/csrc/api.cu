@@ -244,24 +244,47 @@ int forward_simt(const gm_model* m, const float* nodes, const float* edge_attr, 
   return GM_OK;
 }
 
+// per-kernel-class CUDA-event timing of one forward (gm_model_forward_profile): class 0 enc_edge, 1 enc_node,
+// 2 mp_edge, 3 mp_node(+decoder)
+struct FwdProfile {
+  std::vector<cudaEvent_t> ev;
+  std::vector<int> cls;
+  cudaStream_t st;
+  int mark(int c) {
+    cudaEvent_t e;
+    GM_CUDA(cudaEventCreate(&e));
+    GM_CUDA(cudaEventRecord(e, st));
+    ev.push_back(e);
+    cls.push_back(c);
+    return GM_OK;
+  }
+};
+
 int forward_tc(const gm_model* m, const float* nodes, const float* edge_attr, const float* pos, int pos_stride,
                float conn_r, int n_nodes, int max_edges, const int* n_edges_dev, const int* recv_ptr,
                const int* esend, const int* erecv, const int* eref, float* pred, const FwdWs& w,
-               cudaStream_t st) {
+               cudaStream_t st, FwdProfile* prof = nullptr) {
   GM_REQUIRE(m->tc_ok, "model shape (hidden=%d, num_layers=%d) is not covered by the tcgen05 kernels", m->hidden,
              m->num_layers);
   TcGraph g{n_edges_dev, max_edges, n_nodes, esend, erecv, recv_ptr};
   TcBuffers b{w.e, w.v, w.pr, w.ps, w.aggpart, w.carry};
   int rc;
+#define GM_MARK(c) do { if (prof && (rc = prof->mark(c))) return rc; } while (0)
+  GM_MARK(0);
   if ((rc = tc_enc_edge(m->tc_enc_edge, m->edge_dim, pos, pos_stride, conn_r, edge_attr, eref, g, b, st))) return rc;
+  GM_MARK(1);
   if ((rc = tc_enc_node(m->tc_enc_node, m->tc_proc_edge[0], m->node_dim, nodes, g, b, st))) return rc;
   for (int s = 0; s < m->m_steps; ++s) {
+    GM_MARK(2);
     if ((rc = tc_mp_edge(m->tc_proc_edge[s], g, b, st))) return rc;
+    GM_MARK(3);
     const bool last = s + 1 == m->m_steps;
     if ((rc = tc_mp_node(m->tc_proc_node[s], last ? nullptr : &m->tc_proc_edge[s + 1], last ? &m->tc_dec : nullptr,
                          m->out_dim, pred, g, b, st)))
       return rc;
   }
+  GM_MARK(-1);
+#undef GM_MARK
   return GM_OK;
 }
 
@@ -579,6 +602,42 @@ int gm_model_forward(const gm_model* model, int32_t impl, const float* nodes, co
                       recv_ptr, esend, erecv, eref, pred, w, (cudaStream_t)stream);
   return forward_simt(model, nodes, edge_attr, pos, pos_stride, (float)conn_r, n_nodes, max_edges, n_edges_dev,
                       recv_ptr, esend, erecv, eref, pred, w, (cudaStream_t)stream);
+}
+
+int gm_model_forward_profile(const gm_model* model, const float* nodes, const float* edge_attr, const float* pos,
+                             int32_t pos_stride, double conn_r, int32_t n_nodes, int32_t max_edges,
+                             const int32_t* n_edges_dev, const int32_t* recv_ptr, const int32_t* esend,
+                             const int32_t* erecv, const int32_t* eref, float* pred, void* workspace,
+                             size_t workspace_bytes, void* stream, float* ms_host, int32_t* launches_host) {
+  GM_REQUIRE(model != nullptr && nodes != nullptr && pred != nullptr && ms_host != nullptr && launches_host != nullptr,
+             "gm_model_forward_profile: NULL argument");
+  GM_REQUIRE(model->tc_ok, "gm_model_forward_profile: the tcgen05 path does not cover this model shape");
+  GM_REQUIRE(n_nodes > 0 && max_edges >= 0 && n_edges_dev != nullptr, "gm_model_forward_profile: bad sizes");
+  Arena a(workspace, workspace_bytes);
+  FwdWs w;
+  carve_forward(a, model, n_nodes, max_edges, false, w);
+  if (!a.ok || workspace == nullptr) {
+    set_error("gm_model_forward_profile: workspace too small (%zu < %zu bytes)", workspace_bytes, a.off);
+    return GM_ERR_WORKSPACE;
+  }
+  FwdProfile prof;
+  prof.st = (cudaStream_t)stream;
+  int rc = forward_tc(model, nodes, edge_attr, pos, pos_stride, (float)conn_r, n_nodes, max_edges, n_edges_dev,
+                      recv_ptr, esend, erecv, eref, pred, w, prof.st, &prof);
+  cudaError_t ce = cudaStreamSynchronize(prof.st);
+  for (int c = 0; c < 4; ++c) { ms_host[c] = 0.f; launches_host[c] = 0; }
+  if (rc == GM_OK && ce == cudaSuccess) {
+    for (size_t i = 0; i + 1 < prof.ev.size(); ++i) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, prof.ev[i], prof.ev[i + 1]);
+      const int c = prof.cls[i];
+      if (c >= 0 && c < 4) { ms_host[c] += ms; launches_host[c] += 1; }
+    }
+  }
+  for (cudaEvent_t e : prof.ev) cudaEventDestroy(e);
+  if (rc) return rc;
+  if (ce != cudaSuccess) return cuda_fail(ce, "gm_model_forward_profile sync");
+  return GM_OK;
 }
 
 int gm_mlp_forward(int32_t n_layers, const float* const* weights_t, const float* const* biases, const int32_t* dims,

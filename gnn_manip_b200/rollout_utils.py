@@ -112,7 +112,7 @@ class Rollout:
     def reset(self, obs=None, step=0):
         """Restore the initial state (or `obs` [k, n_graphs*N, D]) and set the step counter."""
         with torch.cuda.device(self.device):
-            self.obs.copy_(self.obs0 if obs is None else obs.to(self.device), non_blocking=True)
+            self.obs.copy_(self.obs0 if obs is None else obs.reshape(self.obs.shape), non_blocking=True)
             check(_lib.lib().gm_rollout_reset(self.handle, int(step), stream_ptr(self.device)), "gm_rollout_reset")
 
     def run(self, steps):

@@ -136,6 +136,16 @@ int gm_model_forward(const gm_model* model, int32_t impl, const float* nodes, co
                      const int32_t* erecv, const int32_t* eref, float* pred, void* workspace,
                      size_t workspace_bytes, void* stream);
 
+/* Same forward on the tcgen05 path with a CUDA event recorded on `stream` before every kernel; synchronises the
+ * stream and returns per-kernel-class device time: ms_host[4] / launches_host[4] for
+ * {edge encoder, node encoder, mp_edge (edge MLP + segmented sum), mp_node (node MLP + projections / decoder)}.
+ * Measurement aid for bench.py's roofline (no reference counterpart). */
+int gm_model_forward_profile(const gm_model* model, const float* nodes, const float* edge_attr, const float* pos,
+                             int32_t pos_stride, double conn_r, int32_t n_nodes, int32_t max_edges,
+                             const int32_t* n_edges_dev, const int32_t* recv_ptr, const int32_t* esend,
+                             const int32_t* erecv, const int32_t* eref, float* pred, void* workspace,
+                             size_t workspace_bytes, void* stream, float* ms_host, int32_t* launches_host);
+
 /* Block-level entry points (any widths; fp32 CUDA cores) behind EdgeModel / NodeModel / GraphIndependent:
  * out[m] = MLP(concat_s src[s][idx[s] ? idx[s][m] : m]) with ReLU between layers, optional LayerNorm(eps 1e-5).
  * weights_t[l]: TRANSPOSED Linear weight [in_l, out_l]; all arrays of pointers are HOST arrays of device pointers. */

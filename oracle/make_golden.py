@@ -155,6 +155,10 @@ def main():
     golden_step(ref)
     golden_rollout(ref)
     golden_blocks(ref)
+    # the CMA-ES warm-start control curve (301 x 2 float64 data file, not source): input fixture for bench.py / tests
+    import shutil
+    shutil.copy(os.path.join(ref_shims.REFERENCE_ROOT, "dataset", "sample_traj.npy"),
+                os.path.join(GOLDEN_DIR, "sample_traj.npy"))
 
 
 if __name__ == "__main__":
