@@ -81,6 +81,7 @@ SIGNATURES = {
     "gm_rollout_graph": (ctypes.c_int, [c_void_p] + [POINTER(c_void_p)] * 5),
     "gm_rollout_kernel_launches_per_step": (c_int64, [c_void_p]),
     "gm_rollout_destroy": (None, [c_void_p]),
+    "gm_debug_stamps": (ctypes.c_int, [c_void_p, c_int32]),
     "gm_selftest_gemm": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),
 }
 

@@ -793,6 +793,8 @@ void gm_rollout_destroy(gm_rollout* r) {
   delete r;
 }
 
+int gm_debug_stamps(unsigned long long* out_host, int32_t n) { return tc_debug_stamps(out_host, n); }
+
 int gm_selftest_gemm(const float* x, const float* w, void* chunk, float* out, int32_t M, void* stream) {
   int rc = tc_configure();
   if (rc) return rc;

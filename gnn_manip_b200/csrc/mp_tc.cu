@@ -27,7 +27,7 @@ namespace {
 
 constexpr int NT = 256;                       // 8 warps: (lane quadrant q = warp & 3) x (column half = warp >> 2)
 constexpr uint32_t kIdesc = umma_idesc_bf16(kTile, kH);
-constexpr int kMiscBytes = 24 * 1024;
+constexpr int kMiscBytes = 31 * 1024;
 constexpr int kMaxIn1 = 32;                   // widest SIMT first layer (encoders): node_dim / edge_dim <= 32
 
 struct Misc {                                 // lives after the operand buffers in dynamic smem
@@ -35,12 +35,14 @@ struct Misc {                                 // lives after the operand buffers
   uint64_t bar_mma[2];
   uint32_t tmem_base;
   uint32_t pad;
+  uint32_t segmask[4];                        // bit l of word q: row 32q+l starts a new receiver segment
   int recv[2][kTile];
   int send[2][kTile];
   float red[2][2][kTile];                     // [statistic][column half][row]
   float dot[3][2][kTile];                     // decoder partial dot products
   float b1[kH];
-  float w1[kH * kMaxIn1];                     // fp32 first-layer weights [128][in1]
+  float w1[kH * kMaxIn1];                     // fp32 first-layer weights [128][in1] (encoders)
+  float prm[1536];                            // biases / LayerNorm affine / decoder tail (kPrm* offsets)
 };
 static_assert(sizeof(Misc) <= kMiscBytes, "Misc overflows its shared-memory slot");
 
@@ -62,7 +64,7 @@ __device__ __forceinline__ void ctx_init(Ctx& c, char* smem, int n_a, int tmem_c
   c.q = c.warp & 3;
   c.hf = c.warp >> 2;
   c.row = c.q * 32 + c.lane;
-  char* base = (char*)(((uintptr_t)smem + 1023) & ~(uintptr_t)1023);
+  char* base = smem + ((1024u - (smem_u32(smem) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared state space
   for (int i = 0; i < 2; ++i) {
     c.a[i] = base + (size_t)(i < n_a ? i : 0) * kChunkBytes;
     c.a_s[i] = smem_u32(c.a[i]);
@@ -146,6 +148,15 @@ __device__ __forceinline__ void wait_gemm(Ctx& c, int s) {
   c.ph_mma[s] ^= 1;
   tc_fence_after();
 }
+
+// Phase timestamps of CTA 0 (debug aid, -DGM_STAMPS): thread 0 records clock64() at numbered phases of its
+// second tile; read back with gm_debug_stamps().
+#ifdef GM_STAMPS
+__device__ unsigned long long g_stamps[64];
+#define GM_STAMP(i) do { if (blockIdx.x == 0 && threadIdx.x == 0 && stamp_on) g_stamps[i] = clock64(); } while (0)
+#else
+#define GM_STAMP(i) do { } while (0)
+#endif
 
 // byte offset of logical (row, col8-group) inside a SWIZZLE_128B K-major bf16 image
 __device__ __forceinline__ uint32_t a_off(int row, int col) {
@@ -269,149 +280,417 @@ __device__ __forceinline__ uint32_t s_off(int row, int col) {
 }
 
 // ================================================================================================
-// mp_edge: one message-passing step, edge half, for 2 x 128 edges per CTA iteration.
+// mp_edge: one message-passing step, edge half, one 128-edge tile per CTA iteration.
+//
+// Shared memory: A (bf16 hi/lo operand, 64 KB) | S (fp32 staging tile, 64 KB, s_off swizzle) | W (64 KB).
+// No global-load latency sits inside an epilogue: the sender projections Ps[send] are gathered into S with
+// cp.async (LDGSTS, one coalesced 512 B row per warp instruction) before the first GEMM is issued, the fp32
+// residual rows e are fetched into S the same way while layers 2 and 3 run, and the next layer's weights are
+// streamed by the TMA unit (cp.async.bulk) as soon as the GEMM that used the W buffer has committed.
+// The receiver projections Pr[recv] are read straight from L1/L2: edges are receiver-major, so the ~20
+// consecutive rows of a receiver hit the same 512 B.
 // ================================================================================================
-__global__ void __launch_bounds__(NT, 1) mp_edge_kernel(TcMlp m, TcGraph g, TcBuffers b) {
-  extern __shared__ char smem_raw[];
-  Ctx c;
-  ctx_init(c, smem_raw, 2, 256);
-  const int E = min(*g.n_edges_dev, g.max_edges);
-  const int n_tiles = (E + 2 * kTile - 1) / (2 * kTile);
+constexpr int kPrmB1 = 0, kPrmB2 = 128, kPrmB3 = 256, kPrmG = 384, kPrmB = 512;   // offsets into Misc::w1
 
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int row0 = tile * 2 * kTile;
-    load_w(c, m.wc[0]);
-    // ---- prologue: ids + e tile -> A operands ----
-    for (int i = c.tid; i < 2 * kTile; i += NT) {
-      const int s = i >> 7, r = i & (kTile - 1), ge = row0 + i;
-      c.misc->recv[s][r] = ge < E ? g.erecv[ge] : -1;
-      c.misc->send[s][r] = ge < E ? g.esend[ge] : -1;
-    }
-#pragma unroll 1
-    for (int s = 0; s < 2; ++s) {
-      const int base = row0 + s * kTile;
-      const float* e_in = b.e;
-      load_rows_to_a(c, c.a[s], min(kTile, max(E - base, 0)),
-                     [=](int r) { return e_in + (size_t)(base + r) * kH; });
-    }
-    // ---- layer 1: e We^T + Pr[recv] + Ps[send] + b1 ----
-    launch_gemm(c, 0, 2, false);
-#pragma unroll 1
-    for (int s = 0; s < 2; ++s) {
-      wait_gemm(c, s);
-      if (s == 1) load_w(c, m.wc[1]);
-      const int rid = c.misc->recv[s][c.row], sid = c.misc->send[s][c.row];
-      const float* pa = b.pr + (size_t)(rid < 0 ? 0 : rid) * kH;
-      const float* pb = b.ps + (size_t)(sid < 0 ? 0 : sid) * kH;
-      epi_hidden(c, s, s, m.b1, pa, pb);
-    }
-    // ---- layer 2 ----
-    launch_gemm(c, 0, 2, false);
-#pragma unroll 1
-    for (int s = 0; s < 2; ++s) {
-      wait_gemm(c, s);
-      if (s == 1) load_w(c, m.wc[2]);
-      epi_hidden(c, s, s, m.b2, nullptr, nullptr);
-    }
-    // ---- layer 3 + LayerNorm + residual + receiver-segmented sum ----
-    launch_gemm(c, 0, 2, false);
-#pragma unroll 1
-    for (int s = 0; s < 2; ++s) {
-      wait_gemm(c, s);
-      const int base = row0 + s * kTile;
-      const int rows_valid = min(kTile, max(E - base, 0));
-      float mean, rstd;
-      ln_stats(c, s, m.b3, mean, rstd);
-      char* stage = c.a[s];                      // A[s] is free: its last reader (layer-3 MMA) completed
-      const size_t grow = (size_t)(base + c.row) * kH;
-#pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
-        const int col0 = c.hf * 64 + h * 32;
-        float v[32];
-        ln_apply32(c, s, col0, m.b3, m.ln_g, m.ln_b, mean, rstd, v);
+// warp-per-row cp.async of 16 rows (512 B each) into the swizzled fp32 staging tile
+template <typename SrcRow>
+__device__ __forceinline__ void stage_rows_async(const Ctx& c, uint32_t S_s, const float* safe, SrcRow src_row) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4*>(stage + s_off(c.row, col0 + 4 * j)) =
-              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        if (c.row < rows_valid) {                // e' = LN(...) + e   (epd_gnn.py:104), in place
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            float4* p = reinterpret_cast<float4*>(b.e + grow + col0) + j;
-            float4 o = *p;
-            o.x += v[4 * j]; o.y += v[4 * j + 1]; o.z += v[4 * j + 2]; o.w += v[4 * j + 3];
-            *p = o;
-          }
-        }
-      }
-      __syncthreads();
-      // column-owner pass: thread = (64-row agg tile, column); rows of one receiver are contiguous
-      {
-        const int half = c.tid >> 7, col = c.tid & (kH - 1);
-        const int rb = half * kAggRows, re = min(rb + kAggRows, rows_valid);
-        if (rb < re) {
-          const int* rv = c.misc->recv[s];
-          int cur = rv[rb];
-          bool cont = (base + rb) > g.recv_ptr[cur];     // segment began in an earlier agg tile
-          float acc = 0.f;
-          const size_t agg_tile = (size_t)(base + rb) / kAggRows;
-          for (int r = rb; r < re; ++r) {
-            const int rr = rv[r];
-            if (rr != cur) {
-              if (cont) b.carry[agg_tile * kH + col] = acc; else b.aggpart[(size_t)cur * kH + col] = acc;
-              cont = false; acc = 0.f; cur = rr;
-            }
-            acc += *reinterpret_cast<const float*>(stage + s_off(r, col));
-          }
-          if (cont) b.carry[agg_tile * kH + col] = acc; else b.aggpart[(size_t)cur * kH + col] = acc;
-        }
-      }
-      __syncthreads();                            // staging reads done before the next prologue rewrites A[s]
-    }
+  for (int i = 0; i < kTile / (NT / 32); ++i) {
+    const int r = c.warp * (kTile / (NT / 32)) + i;
+    const float* src = src_row(r, i);                       // nullptr -> zero fill
+    cp_async16(S_s + s_off(r, 4 * c.lane), src ? src + 4 * c.lane : safe, src ? 16u : 0u);
   }
-  ctx_fini(c, 256);
+  cp_async_commit();
 }
 
-// ================================================================================================
-// Shared tail of the node kernels: v' (already split into A[0]) -> Pr, Ps of the next edge MLP, or decoder.
-// ================================================================================================
-__device__ __forceinline__ void store_d_rows(const Ctx& c, int sub, float* __restrict__ out, int node0,
-                                             int rows_valid) {
-#pragma unroll 1
+// 16 rows per warp, all loads in flight before the first conversion
+template <typename RowPtr>
+__device__ __forceinline__ void load_rows_to_a16(const Ctx& c, char* a, int rows_valid, RowPtr rowptr) {
+  constexpr int R = kTile / (NT / 32);
+  float4 x[R];
+#pragma unroll
+  for (int i = 0; i < R; ++i) {
+    const int r = c.warp * R + i;
+    x[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < rows_valid) x[i] = __ldg(reinterpret_cast<const float4*>(rowptr(r)) + c.lane);
+  }
+#pragma unroll
+  for (int i = 0; i < R; ++i) {
+    const int r = c.warp * R + i;
+    uint2 hi, lo;
+    split_bf16x2(x[i].x, x[i].y, hi.x, lo.x);
+    split_bf16x2(x[i].z, x[i].w, hi.y, lo.y);
+    const uint32_t o = a_off(r, 4 * c.lane);
+    *reinterpret_cast<uint2*>(a + o) = hi;
+    *reinterpret_cast<uint2*>(a + kImageBytes + o) = lo;
+  }
+}
+
+// hidden-layer epilogue with the bias in shared memory: A <- split(relu(D + bias))
+__device__ __forceinline__ void epi_hidden_s(const Ctx& c, char* a, const float* __restrict__ bias_s) {
+#pragma unroll
   for (int h = 0; h < 2; ++h) {
     const int col0 = c.hf * 64 + h * 32;
     float v[32];
-    tmem_ld32(d_addr(c, sub, col0), v);
+    tmem_ld32(d_addr(c, 0, col0), v);
     tmem_ld_wait();
-    if (c.row < rows_valid) {
-      float4* p = reinterpret_cast<float4*>(out + (size_t)(node0 + c.row) * kH + col0);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) p[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    for (int j = 0; j < 8; ++j) {
+      const float4 bs = *reinterpret_cast<const float4*>(bias_s + col0 + 4 * j);
+      v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f); v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
+      v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f); v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w, 0.f);
     }
+#pragma unroll
+    for (int gq = 0; gq < 4; ++gq) store_a8(a, c.row, col0 + 8 * gq, v + 8 * gq);
   }
 }
 
-// expects: load_w(next chunk 0) already issued, A[0] holds split(v').
-__device__ __forceinline__ void node_tail(Ctx& c, const TcMlp* next_edge, const TcMlp* dec, int out_dim,
-                                          float* __restrict__ pred, const TcBuffers& b, int node0, int rows_valid) {
-  if (dec == nullptr) {
-    // Pr = v' Wr^T, Ps = v' Ws^T  (receiver / sender blocks of the next phi_edge first layer)
+// first edge layer: A <- split(relu(D + b1 + Pr[recv] + Ps[send])); Ps rows sit in the staging tile S, this thread's
+// 64 columns of Pr[recv] start at pr_row (first 32 already in p0, loaded while the GEMM ran)
+__device__ __forceinline__ void epi_l1(const Ctx& c, char* a, const float* __restrict__ bias_s, const char* S,
+                                       const float* __restrict__ pr_row, const float4* p0) {
+  float4 p1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) p1[j] = __ldg(reinterpret_cast<const float4*>(pr_row + 32) + j);
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int col0 = c.hf * 64 + h * 32;
+    float v[32];
+    tmem_ld32(d_addr(c, 0, col0), v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 bs = *reinterpret_cast<const float4*>(bias_s + col0 + 4 * j);
+      const float4 s4 = *reinterpret_cast<const float4*>(S + s_off(c.row, col0 + 4 * j));
+      const float4 p = h == 0 ? p0[j] : p1[j];
+      v[4 * j] = fmaxf(v[4 * j] + bs.x + (p.x + s4.x), 0.f);
+      v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y + (p.y + s4.y), 0.f);
+      v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z + (p.z + s4.z), 0.f);
+      v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w + (p.w + s4.w), 0.f);
+    }
+#pragma unroll
+    for (int gq = 0; gq < 4; ++gq) store_a8(a, c.row, col0 + 8 * gq, v + 8 * gq);
+  }
+}
+
+// LayerNorm of this thread's half row of D (+ bias): x[64] <- LN(D + b3) * g + b.  The two column halves of a row
+// live in warps q and q + 4; they exchange their partial sums through shared memory and a 64-thread named barrier.
+__device__ __forceinline__ void ln_row64(const Ctx& c, const float* __restrict__ prm, float* x) {
+  tmem_ld32(d_addr(c, 0, c.hf * 64), x);
+  tmem_ld32(d_addr(c, 0, c.hf * 64 + 32), x + 32);
+  tmem_ld_wait();
+  const float* b3 = prm + kPrmB3 + c.hf * 64;
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float4 t = *reinterpret_cast<const float4*>(b3 + 4 * j);
+    x[4 * j] += t.x; x[4 * j + 1] += t.y; x[4 * j + 2] += t.z; x[4 * j + 3] += t.w;
+    s += (x[4 * j] + x[4 * j + 1]) + (x[4 * j + 2] + x[4 * j + 3]);
+  }
+  c.misc->red[0][c.hf][c.row] = s;
+  named_bar_sync(1 + c.q, 64);
+  const float mean = (c.misc->red[0][0][c.row] + c.misc->red[0][1][c.row]) * (1.0f / kH);
+  float ss = 0.f;
+#pragma unroll
+  for (int j = 0; j < 64; ++j) {
+    x[j] -= mean;
+    ss = fmaf(x[j], x[j], ss);
+  }
+  c.misc->red[1][c.hf][c.row] = ss;
+  named_bar_sync(1 + c.q, 64);
+  const float var = (c.misc->red[1][0][c.row] + c.misc->red[1][1][c.row]) * (1.0f / kH);
+  const float rstd = 1.0f / sqrtf(var + 1e-5f);
+  const float* gg = prm + kPrmG + c.hf * 64;
+  const float* bb = prm + kPrmB + c.hf * 64;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float4 g4 = *reinterpret_cast<const float4*>(gg + 4 * j);
+    const float4 b4 = *reinterpret_cast<const float4*>(bb + 4 * j);
+    x[4 * j] = x[4 * j] * rstd * g4.x + b4.x;
+    x[4 * j + 1] = x[4 * j + 1] * rstd * g4.y + b4.y;
+    x[4 * j + 2] = x[4 * j + 2] * rstd * g4.z + b4.z;
+    x[4 * j + 3] = x[4 * j + 3] * rstd * g4.w + b4.w;
+  }
+}
+
+__device__ __forceinline__ void stage_params(const Ctx& c, const TcMlp& m) {
+  float* prm = c.misc->prm;
+  for (int i = c.tid; i < kH; i += NT) {
+    prm[kPrmB1 + i] = m.b1[i];
+    prm[kPrmB2 + i] = m.b2[i];
+    prm[kPrmB3 + i] = m.b3[i];
+    prm[kPrmG + i] = m.ln_g[i];
+    prm[kPrmB + i] = m.ln_b[i];
+  }
+}
+
+__global__ void __launch_bounds__(NT, 1) mp_edge_kernel(TcMlp m, TcGraph g, TcBuffers b) {
+  extern __shared__ char smem_raw[];
+  Ctx c;
+  ctx_init(c, smem_raw, 2, 128);
+  char* A = c.a[0];
+  char* S = c.a[1];
+  const uint32_t S_s = c.a_s[1];
+  const float* prm = c.misc->prm;
+  stage_params(c, m);                              // published by the first launch_gemm barrier
+  const int E = min(*g.n_edges_dev, g.max_edges);
+  const int n_tiles = (E + kTile - 1) / kTile;
+  constexpr int R = kTile / (NT / 32);             // rows staged per warp
+
+  // Per-tile inputs that are fetched one tile ahead (registers): ids of this thread's row, the sender ids of the
+  // rows this warp stages, and this lane's 16 B of each of those rows of e.
+  int nx_recv = -1, nx_prev = -2, nx_send = -1;
+  float4 ereg[R];
+  auto fetch_ids = [&](int t) {
+    const int r0 = t * kTile, valid = min(kTile, E - r0);
+    nx_recv = c.row < valid ? __ldg(g.erecv + r0 + c.row) : -1;
+    nx_prev = (c.lane == 0 && c.row < valid && r0 + c.row > 0) ? __ldg(g.erecv + r0 + c.row - 1) : -2;
+    const int rl = c.warp * R + (c.lane & (R - 1));
+    nx_send = rl < valid ? __ldg(g.esend + r0 + rl) : -1;
+  };
+  auto fetch_rows = [&](int t) {
+    const int r0 = t * kTile, valid = min(kTile, E - r0);
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+      const int r = c.warp * R + i;
+      ereg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r < valid) ereg[i] = __ldg(reinterpret_cast<const float4*>(b.e + (size_t)(r0 + r) * kH) + c.lane);
+    }
+  };
+  if ((int)blockIdx.x < n_tiles) {
+    load_w(c, m.wc[0]);
+    fetch_ids(blockIdx.x);
+    fetch_rows(blockIdx.x);
+  }
+
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int row0 = tile * kTile;
+    const int rows_valid = min(kTile, E - row0);
+    const bool has_next = tile + (int)gridDim.x < n_tiles;
+#ifdef GM_STAMPS
+    const bool stamp_on = tile == (int)blockIdx.x + (int)gridDim.x;
+#endif
+    GM_STAMP(0);
+    // ---- prologue: ids -> smem, Ps[send] rows -> S (async), e rows (registers) -> A operand ----
+    const int my_recv = nx_recv;
+    if (c.hf == 0) {
+      c.misc->recv[0][c.row] = my_recv;
+      int prev = __shfl_up_sync(0xffffffffu, my_recv, 1);
+      if (c.lane == 0) prev = nx_prev;
+      const unsigned mk = __ballot_sync(0xffffffffu, my_recv != prev);
+      if (c.lane == 0) c.misc->segmask[c.q] = mk;
+    }
+    {
+      const int sid_l = nx_send;
+      const float* ps = b.ps;
+      stage_rows_async(c, S_s, ps, [=](int, int i) -> const float* {
+        const int sid = __shfl_sync(0xffffffffu, sid_l, i);
+        return sid >= 0 ? ps + (size_t)sid * kH : nullptr;
+      });
+    }
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+      uint2 hi, lo;
+      split_bf16x2(ereg[i].x, ereg[i].y, hi.x, lo.x);
+      split_bf16x2(ereg[i].z, ereg[i].w, hi.y, lo.y);
+      const uint32_t o = a_off(c.warp * R + i, 4 * c.lane);
+      *reinterpret_cast<uint2*>(A + o) = hi;
+      *reinterpret_cast<uint2*>(A + kImageBytes + o) = lo;
+    }
+    if (has_next) fetch_ids(tile + gridDim.x);
+    GM_STAMP(1);
+    // ---- layer 1: e We^T + Pr[recv] + Ps[send] + b1 ----
     launch_gemm(c, 0, 1, false);
+    GM_STAMP(2);
+    const float* pr_row = b.pr + (size_t)(my_recv < 0 ? 0 : my_recv) * kH + c.hf * 64;
+    float4 p0[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) p0[j] = __ldg(reinterpret_cast<const float4*>(pr_row) + j);
+    cp_async_wait_all();
+    __syncthreads();                               // every warp's share of the Ps gather is visible
+    GM_STAMP(3);
     wait_gemm(c, 0);
-    load_w(c, next_edge->wc[4]);
-    store_d_rows(c, 0, b.pr, node0, rows_valid);
+    GM_STAMP(4);
+    load_w(c, m.wc[1]);
+    epi_l1(c, A, prm + kPrmB1, S, pr_row, p0);
+    GM_STAMP(5);
+    // ---- layer 2; the fp32 residual rows travel into S meanwhile ----
     launch_gemm(c, 0, 1, false);
+    {
+      const float* e_in = b.e;
+      stage_rows_async(c, S_s, e_in, [=](int r, int) -> const float* {
+        return r < rows_valid ? e_in + (size_t)(row0 + r) * kH : nullptr;
+      });
+    }
+    GM_STAMP(6);
     wait_gemm(c, 0);
-    store_d_rows(c, 0, b.ps, node0, rows_valid);
+    GM_STAMP(7);
+    load_w(c, m.wc[2]);
+    epi_hidden_s(c, A, prm + kPrmB2);
+    GM_STAMP(8);
+    // ---- layer 3 + LayerNorm + residual + receiver-segmented sum ----
+    cp_async_wait_all();
+    launch_gemm(c, 0, 1, false);
+    GM_STAMP(9);
+    wait_gemm(c, 0);
+    GM_STAMP(10);
+    if (has_next) load_w(c, m.wc[0]);              // next tile's first layer
+    {
+      float x[64];
+      ln_row64(c, prm, x);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const uint32_t o = s_off(c.row, c.hf * 64 + 4 * j);
+        float4* sp = reinterpret_cast<float4*>(S + o);
+        const float4 e4 = *sp;
+        *sp = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);   // pre-residual output for the sum
+        *reinterpret_cast<float4*>(A + o) =                                       // e' = LN(...) + e (epd_gnn.py:104)
+            make_float4(x[4 * j] + e4.x, x[4 * j + 1] + e4.y, x[4 * j + 2] + e4.z, x[4 * j + 3] + e4.w);
+      }
+    }
+    GM_STAMP(11);
+    tc_fence_before();
+    __syncthreads();
+    GM_STAMP(12);
+    // e' leaves through the A region: one coalesced 512 B row per warp instruction
+    {
+      float4 o4[R];
+#pragma unroll
+      for (int i = 0; i < R; ++i) o4[i] = *reinterpret_cast<const float4*>(A + s_off(c.warp * R + i, 4 * c.lane));
+#pragma unroll
+      for (int i = 0; i < R; ++i) {
+        const int r = c.warp * R + i;
+        if (r < rows_valid) reinterpret_cast<float4*>(b.e + (size_t)(row0 + r) * kH)[c.lane] = o4[i];
+      }
+    }
+    if (has_next) fetch_rows(tile + gridDim.x);    // in flight during the column pass
+    GM_STAMP(15);
+    // column-owner pass: thread = (64-row agg tile, column).  Rows of one receiver are contiguous; the segment
+    // starts come from the bit masks, so control flow is uniform and the row loads are independent.
+    {
+      const int half = c.tid >> 7, col = c.tid & (kH - 1);
+      const int rb = half * kAggRows;
+      const int nrows = min(kAggRows, rows_valid - rb);
+      if (nrows > 0) {
+        const unsigned long long mask =
+            ((unsigned long long)c.misc->segmask[2 * half + 1] << 32) | c.misc->segmask[2 * half];
+        const int* rv = c.misc->recv[0] + rb;
+        bool cont = !(mask & 1ull);                  // row rb continues the receiver of the edge before it
+        const size_t agg_tile = (size_t)(row0 + rb) / kAggRows;
+        int r = 0;
+        while (r < nrows) {
+          const unsigned long long rest = r + 1 < 64 ? (mask >> (r + 1)) : 0ull;
+          const int end = min(rest ? r + __ffsll((long long)rest) : 64, nrows);
+          const int rid = rv[r];
+          float acc = 0.f;
+          int i = r;
+#pragma unroll 1
+          for (; i + 4 <= end; i += 4) {
+            const float y0 = *reinterpret_cast<const float*>(S + s_off(rb + i, col));
+            const float y1 = *reinterpret_cast<const float*>(S + s_off(rb + i + 1, col));
+            const float y2 = *reinterpret_cast<const float*>(S + s_off(rb + i + 2, col));
+            const float y3 = *reinterpret_cast<const float*>(S + s_off(rb + i + 3, col));
+            acc += y0; acc += y1; acc += y2; acc += y3;
+          }
+          for (; i < end; ++i) acc += *reinterpret_cast<const float*>(S + s_off(rb + i, col));
+          if (cont) b.carry[agg_tile * kH + col] = acc; else b.aggpart[(size_t)rid * kH + col] = acc;
+          cont = false;
+          r = end;
+        }
+      }
+    }
+    GM_STAMP(13);
+    __syncthreads();                                // S and recv[] are rewritten by the next tile's prologue
+    GM_STAMP(14);
+  }
+  ctx_fini(c, 128);
+}
+
+// ================================================================================================
+// Node kernels.  Shared memory: A0 (bf16 hi/lo operand) | T (second operand during layer 1, then the fp32
+// staging tile in s_off layout) | W.  Everything that leaves or enters through global memory moves as coalesced
+// 512 B rows: the residual v rows arrive in T by cp.async while layers 2 and 3 run, and v', Pr, Ps leave
+// through T with one row per warp instruction.
+// ================================================================================================
+constexpr int kPrmD1 = 640, kPrmD2 = 768, kPrmW3 = 896, kPrmD3 = 1280;   // decoder b1, b2, w3 [3][128], b3 [3]
+
+// T (fp32, s_off layout) -> global rows [row0, row0 + rows_valid) of a [*, 128] matrix
+__device__ __forceinline__ void copy_out_rows(const Ctx& c, const char* T, float* __restrict__ out, int row0,
+                                              int rows_valid) {
+  constexpr int R = kTile / (NT / 32);
+  float4 o4[R];
+#pragma unroll
+  for (int i = 0; i < R; ++i) o4[i] = *reinterpret_cast<const float4*>(T + s_off(c.warp * R + i, 4 * c.lane));
+#pragma unroll
+  for (int i = 0; i < R; ++i) {
+    const int r = c.warp * R + i;
+    if (r < rows_valid) reinterpret_cast<float4*>(out + (size_t)(row0 + r) * kH)[c.lane] = o4[i];
+  }
+}
+
+// this thread's half row of D -> T
+__device__ __forceinline__ void d_to_stage(const Ctx& c, char* T) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int col0 = c.hf * 64 + h * 32;
+    float v[32];
+    tmem_ld32(d_addr(c, 0, col0), v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<float4*>(T + s_off(c.row, col0 + 4 * j)) =
+          make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+  }
+}
+
+// From "layer-3 accumulator complete" to the end of the tile.  Expects the weight chunk of the following GEMM
+// (Wr of the next edge MLP, or the decoder's first layer) already on its way into W.
+//   v' = LN(D + b3) (+ v rows waiting in T)  -> global v (through T) and, split, -> A0
+//   then Pr = v' Wr^T, Ps = v' Ws^T -> global (through T), or the decoder -> pred.
+__device__ __forceinline__ void node_finish(Ctx& c, char* A0, char* T, const float* __restrict__ prm, bool residual,
+                                            const TcMlp& next, bool has_dec, int out_dim, float* __restrict__ pred,
+                                            const TcBuffers& b, int node0, int rows_valid) {
+  {
+    float x[64];
+    ln_row64(c, prm, x);
+    const bool live = c.row < rows_valid;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float4* sp = reinterpret_cast<float4*>(T + s_off(c.row, c.hf * 64 + 4 * j));
+      if (residual) {                                  // v' = LN(...) + v   (epd_gnn.py:103)
+        const float4 o = *sp;
+        x[4 * j] += o.x; x[4 * j + 1] += o.y; x[4 * j + 2] += o.z; x[4 * j + 3] += o.w;
+      }
+      if (!live) x[4 * j] = x[4 * j + 1] = x[4 * j + 2] = x[4 * j + 3] = 0.f;
+      *sp = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+    }
+#pragma unroll
+    for (int gq = 0; gq < 8; ++gq) store_a8(A0, c.row, c.hf * 64 + 8 * gq, x + 8 * gq);
+  }
+  launch_gemm(c, 0, 1, false);                         // v' Wr^T   |   decoder layer 1
+  copy_out_rows(c, T, b.v, node0, rows_valid);         // overlaps the GEMM
+  wait_gemm(c, 0);
+  if (!has_dec) {
+    load_w(c, next.wc[4]);
+    __syncthreads();                                   // every warp is done reading v' out of T
+    d_to_stage(c, T);
+    launch_gemm(c, 0, 1, false);                       // v' Ws^T
+    copy_out_rows(c, T, b.pr, node0, rows_valid);
+    wait_gemm(c, 0);
+    __syncthreads();
+    d_to_stage(c, T);
+    tc_fence_before();
+    __syncthreads();
+    copy_out_rows(c, T, b.ps, node0, rows_valid);
   } else {
-    // decoder: Linear+ReLU, Linear+ReLU on the tensor cores, Linear(128 -> out_dim) with CUDA cores
-    launch_gemm(c, 0, 1, false);
-    wait_gemm(c, 0);
-    load_w(c, dec->wc[1]);
-    epi_hidden(c, 0, 0, dec->b1, nullptr, nullptr);
+    // decoder: Linear+ReLU, Linear+ReLU on the tensor cores, Linear(128 -> out_dim) on CUDA cores (epd_gnn.py:49,96)
+    load_w(c, next.wc[1]);
+    epi_hidden_s(c, A0, prm + kPrmD1);
     launch_gemm(c, 0, 1, false);
     wait_gemm(c, 0);
     float acc[3] = {0.f, 0.f, 0.f};
-#pragma unroll 1
+#pragma unroll
     for (int h = 0; h < 2; ++h) {
       const int col0 = c.hf * 64 + h * 32;
       float v[32];
@@ -419,62 +698,33 @@ __device__ __forceinline__ void node_tail(Ctx& c, const TcMlp* next_edge, const 
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
-        const float x = fmaxf(v[j] + __ldg(dec->b2 + col0 + j), 0.f);
+        const float x = fmaxf(v[j] + prm[kPrmD2 + col0 + j], 0.f);
 #pragma unroll
-        for (int o = 0; o < 3; ++o)
-          if (o < out_dim) acc[o] = fmaf(x, __ldg(dec->w3 + o * kH + col0 + j), acc[o]);
+        for (int o = 0; o < 3; ++o) acc[o] = fmaf(x, prm[kPrmW3 + o * kH + col0 + j], acc[o]);
       }
     }
 #pragma unroll
     for (int o = 0; o < 3; ++o) c.misc->dot[o][c.hf][c.row] = acc[o];
+    tc_fence_before();
     __syncthreads();
     if (c.hf == 0 && c.row < rows_valid) {
       for (int o = 0; o < out_dim; ++o)
         pred[(size_t)(node0 + c.row) * out_dim + o] =
-            c.misc->dot[o][0][c.row] + c.misc->dot[o][1][c.row] + __ldg(dec->b3 + o);
+            c.misc->dot[o][0][c.row] + c.misc->dot[o][1][c.row] + prm[kPrmD3 + o];
     }
-    __syncthreads();
   }
+  tc_fence_before();
+  __syncthreads();                                     // T, A0, dot[] and D are reused by the next tile
 }
 
-// layers 2,3 + LayerNorm (+ residual) of a node MLP whose layer-1 pre-activation sits in D[0];
-// leaves v' in global memory and split(v') in A[0]; issues the load of `next_chunk`.
-__device__ __forceinline__ void node_body(Ctx& c, const TcMlp& m, const void* next_chunk, bool residual,
-                                          const TcBuffers& b, int node0, int rows_valid) {
-  load_w(c, m.wc[2]);
-  epi_hidden(c, 0, 0, m.b1, nullptr, nullptr);
-  launch_gemm(c, 0, 1, false);
-  wait_gemm(c, 0);
-  load_w(c, m.wc[3]);
-  epi_hidden(c, 0, 0, m.b2, nullptr, nullptr);
-  launch_gemm(c, 0, 1, false);
-  wait_gemm(c, 0);
-  load_w(c, next_chunk);
-  float mean, rstd;
-  ln_stats(c, 0, m.b3, mean, rstd);
-  const size_t grow = (size_t)(node0 + c.row) * kH;
-#pragma unroll 1
-  for (int h = 0; h < 2; ++h) {
-    const int col0 = c.hf * 64 + h * 32;
-    float v[32];
-    ln_apply32(c, 0, col0, m.b3, m.ln_g, m.ln_b, mean, rstd, v);
-    if (c.row < rows_valid) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float4* p = reinterpret_cast<float4*>(b.v + grow + col0) + j;
-        if (residual) {                         // v' = LN(...) + v   (epd_gnn.py:103), in place
-          const float4 o = *p;
-          v[4 * j] += o.x; v[4 * j + 1] += o.y; v[4 * j + 2] += o.z; v[4 * j + 3] += o.w;
-        }
-        *p = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = 0.f;
-    }
-#pragma unroll
-    for (int gq = 0; gq < 4; ++gq) store_a8(c.a[0], c.row, col0 + 8 * gq, v + 8 * gq);
+__device__ __forceinline__ void stage_dec_params(const Ctx& c, const TcMlp& dec, int out_dim) {
+  float* prm = c.misc->prm;
+  for (int i = c.tid; i < kH; i += NT) {
+    prm[kPrmD1 + i] = dec.b1[i];
+    prm[kPrmD2 + i] = dec.b2[i];
   }
+  for (int i = c.tid; i < 3 * kH; i += NT) prm[kPrmW3 + i] = i < out_dim * kH ? dec.w3[i] : 0.f;
+  if (c.tid < 3) prm[kPrmD3 + c.tid] = c.tid < out_dim ? dec.b3[c.tid] : 0.f;
 }
 
 // ================================================================================================
@@ -486,46 +736,81 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
   extern __shared__ char smem_raw[];
   Ctx c;
   ctx_init(c, smem_raw, 2, 128);
+  char* A0 = c.a[0];
+  char* T = c.a[1];
+  const uint32_t T_s = c.a_s[1];
+  const float* prm = c.misc->prm;
+  stage_params(c, m);
+  if (has_dec) stage_dec_params(c, next, out_dim);
+  constexpr int R = kTile / (NT / 32);
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
+  if ((int)blockIdx.x < n_tiles) load_w(c, m.wc[0]);
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
-    load_w(c, m.wc[0]);
-    // A[0] <- total aggregate per node = first-tile partial + carries of the following agg tiles
-#pragma unroll 2
-    for (int r = c.warp; r < kTile; r += NT / 32) {
-      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (r < rows_valid) {
-        const int n = node0 + r;
-        const int sb = g.recv_ptr[n], se = g.recv_ptr[n + 1];
-        if (se > sb) {
-          x = __ldg(reinterpret_cast<const float4*>(b.aggpart + (size_t)n * kH) + c.lane);
-          const int t0 = sb / kAggRows, t1 = (se - 1) / kAggRows;
+    // ---- prologue: total aggregate per node (first-tile partial + carries of the following agg tiles) -> A0,
+    //      node latents -> T (as the second layer-1 operand) ----
+    {
+      const int nl = min(node0 + c.warp * R + min(c.lane, R), g.n_nodes);
+      const int rp = __ldg(g.recv_ptr + nl);
+      float4 x[R];
+      int sb[R], se[R];
+#pragma unroll
+      for (int i = 0; i < R; ++i) {
+        const int r = c.warp * R + i;
+        sb[i] = __shfl_sync(0xffffffffu, rp, i);
+        se[i] = __shfl_sync(0xffffffffu, rp, i + 1);
+        x[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r >= rows_valid) se[i] = sb[i];
+        if (se[i] > sb[i]) x[i] = __ldg(reinterpret_cast<const float4*>(b.aggpart + (size_t)(node0 + r) * kH) + c.lane);
+      }
+#pragma unroll
+      for (int i = 0; i < R; ++i) {
+        if (se[i] > sb[i]) {
+          const int t0 = sb[i] / kAggRows, t1 = (se[i] - 1) / kAggRows;
           for (int t = t0 + 1; t <= t1; ++t) {
             const float4 y = __ldg(reinterpret_cast<const float4*>(b.carry + (size_t)t * kH) + c.lane);
-            x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+            x[i].x += y.x; x[i].y += y.y; x[i].z += y.z; x[i].w += y.w;
           }
         }
+        uint2 hi, lo;
+        split_bf16x2(x[i].x, x[i].y, hi.x, lo.x);
+        split_bf16x2(x[i].z, x[i].w, hi.y, lo.y);
+        const uint32_t o = a_off(c.warp * R + i, 4 * c.lane);
+        *reinterpret_cast<uint2*>(A0 + o) = hi;
+        *reinterpret_cast<uint2*>(A0 + kImageBytes + o) = lo;
       }
-      uint2 hi, lo;
-      split_bf16x2(x.x, x.y, hi.x, lo.x);
-      split_bf16x2(x.z, x.w, hi.y, lo.y);
-      const uint32_t o = a_off(r, 4 * c.lane);
-      *reinterpret_cast<uint2*>(c.a[0] + o) = hi;
-      *reinterpret_cast<uint2*>(c.a[0] + kImageBytes + o) = lo;
     }
     {
       const float* v_in = b.v;
-      load_rows_to_a(c, c.a[1], rows_valid, [=](int r) { return v_in + (size_t)(node0 + r) * kH; });
+      load_rows_to_a16(c, T, rows_valid, [=](int r) { return v_in + (size_t)(node0 + r) * kH; });
     }
-    launch_gemm(c, 0, 1, false);     // agg @ W1a^T
+    // ---- layer 1: agg W1a^T + v W1b^T ----
+    launch_gemm(c, 0, 1, false);
     wait_gemm(c, 0);
     load_w(c, m.wc[1]);
-    launch_gemm(c, 1, 1, true);      // + v @ W1b^T   (A[1], same accumulator)
-    // note: launch_gemm(c, 1, ...) maps sub 0 -> A[1], TMEM cols 0
+    launch_gemm(c, 1, 1, true);                    // sub 0 of launch_gemm(c, 1, ...) reads A buffer 1 (= T), TMEM cols 0
     wait_gemm(c, 0);
-    node_body(c, m, has_dec ? next.wc[0] : next.wc[3], true, b, node0, rows_valid);
-    node_tail(c, &next, has_dec ? &next : nullptr, out_dim, pred, b, node0, rows_valid);
+    load_w(c, m.wc[2]);
+    {                                              // T is free: the fp32 residual rows travel into it meanwhile
+      const float* v_in = b.v;
+      stage_rows_async(c, T_s, v_in, [=](int r, int) -> const float* {
+        return r < rows_valid ? v_in + (size_t)(node0 + r) * kH : nullptr;
+      });
+    }
+    epi_hidden_s(c, A0, prm + kPrmB1);
+    // ---- layer 2 ----
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    load_w(c, m.wc[3]);
+    epi_hidden_s(c, A0, prm + kPrmB2);
+    // ---- layer 3 + LayerNorm + residual, then the projections for the next edge step or the decoder ----
+    cp_async_wait_all();
+    launch_gemm(c, 0, 1, false);
+    wait_gemm(c, 0);
+    load_w(c, has_dec ? next.wc[0] : next.wc[3]);
+    node_finish(c, A0, T, prm, true, next, has_dec != 0, out_dim, pred, b, node0, rows_valid);
+    if (tile + (int)gridDim.x < n_tiles) load_w(c, m.wc[0]);
   }
   ctx_fini(c, 128);
 }
@@ -537,15 +822,18 @@ __global__ void __launch_bounds__(NT, 1)
 enc_node_kernel(TcMlp m, TcMlp next, int node_dim, const float* __restrict__ nodes, TcGraph g, TcBuffers b) {
   extern __shared__ char smem_raw[];
   Ctx c;
-  ctx_init(c, smem_raw, 1, 128);
+  ctx_init(c, smem_raw, 2, 128);
+  char* A0 = c.a[0];
+  char* T = c.a[1];
+  const float* prm = c.misc->prm;
+  stage_params(c, m);
   for (int i = c.tid; i < kH * node_dim; i += NT) c.misc->w1[i] = m.w1[i];
-  for (int i = c.tid; i < kH; i += NT) c.misc->b1[i] = m.b1[i];
   __syncthreads();
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
+  if ((int)blockIdx.x < n_tiles) load_w(c, m.wc[2]);
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
-    load_w(c, m.wc[2]);
     float x[kMaxIn1];
 #pragma unroll
     for (int k = 0; k < kMaxIn1; ++k)
@@ -556,43 +844,24 @@ enc_node_kernel(TcMlp m, TcMlp next, int node_dim, const float* __restrict__ nod
       float h[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        float acc = c.misc->b1[col0 + j];
+        float acc = prm[kPrmB1 + col0 + j];
         const float* w = c.misc->w1 + (size_t)(col0 + j) * node_dim;
 #pragma unroll
         for (int k = 0; k < kMaxIn1; ++k)
           if (k < node_dim) acc = fmaf(x[k], w[k], acc);
         h[j] = fmaxf(acc, 0.f);
       }
-      store_a8(c.a[0], c.row, col0, h);
+      store_a8(A0, c.row, col0, h);
     }
     launch_gemm(c, 0, 1, false);
     wait_gemm(c, 0);
     load_w(c, m.wc[3]);
-    epi_hidden(c, 0, 0, m.b2, nullptr, nullptr);
+    epi_hidden_s(c, A0, prm + kPrmB2);
     launch_gemm(c, 0, 1, false);
     wait_gemm(c, 0);
     load_w(c, next.wc[3]);
-    float mean, rstd;
-    ln_stats(c, 0, m.b3, mean, rstd);
-    const size_t grow = (size_t)(node0 + c.row) * kH;
-#pragma unroll 1
-    for (int hh = 0; hh < 2; ++hh) {
-      const int col0 = c.hf * 64 + hh * 32;
-      float v[32];
-      ln_apply32(c, 0, col0, m.b3, m.ln_g, m.ln_b, mean, rstd, v);
-      if (c.row < rows_valid) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          reinterpret_cast<float4*>(b.v + grow + col0)[j] =
-              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = 0.f;
-      }
-#pragma unroll
-      for (int gq = 0; gq < 4; ++gq) store_a8(c.a[0], c.row, col0 + 8 * gq, v + 8 * gq);
-    }
-    node_tail(c, &next, nullptr, 0, nullptr, b, node0, rows_valid);
+    node_finish(c, A0, T, prm, false, next, false, 0, nullptr, b, node0, rows_valid);
+    if (tile + (int)gridDim.x < n_tiles) load_w(c, m.wc[2]);
   }
   ctx_fini(c, 128);
 }
@@ -696,7 +965,10 @@ selftest_gemm_kernel(const float* __restrict__ x, const void* chunk, float* __re
     load_rows_to_a(c, c.a[0], kTile, [=](int r) { return x + (size_t)(row0 + r) * kH; });
     launch_gemm(c, 0, 1, false);
     wait_gemm(c, 0);
-    store_d_rows(c, 0, out, row0, kTile);
+    d_to_stage(c, c.a[0]);                           // A[0] is free: the MMA that read it has completed
+    tc_fence_before();
+    __syncthreads();
+    copy_out_rows(c, c.a[0], out, row0, kTile);
     __syncthreads();
   }
   ctx_fini(c, 128);
@@ -719,11 +991,22 @@ int tc_configure() {
   int rc;
   if ((rc = set_smem(mp_edge_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(mp_node_kernel, smem_bytes(2)))) return rc;
-  if ((rc = set_smem(enc_node_kernel, smem_bytes(1)))) return rc;
+  if ((rc = set_smem(enc_node_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(enc_edge_kernel, smem_bytes(1)))) return rc;
   if ((rc = set_smem(selftest_gemm_kernel, smem_bytes(1)))) return rc;
   done = true;
   return GM_OK;
+}
+
+int tc_debug_stamps(unsigned long long* out_host, int n) {
+#ifdef GM_STAMPS
+  GM_CUDA(cudaMemcpyFromSymbol(out_host, g_stamps, sizeof(unsigned long long) * (n < 64 ? n : 64)));
+  return GM_OK;
+#else
+  (void)out_host; (void)n;
+  set_error("library built without -DGM_STAMPS");
+  return GM_ERR_UNSUPPORTED;
+#endif
 }
 
 int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_t stream) {
@@ -731,7 +1014,7 @@ int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_
   const size_t sm = smem_bytes(2);
   int rc = tc_configure();
   if (rc) return rc;
-  const int grid = min(ceil_div(g.max_edges, 2 * kTile), kNumSMs);
+  const int grid = min(ceil_div(g.max_edges, kTile), kNumSMs);
   mp_edge_kernel<<<grid, NT, sm, stream>>>(m, g, b);
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("mp_edge_kernel");
@@ -755,7 +1038,7 @@ int tc_mp_node(const TcMlp& m, const TcMlp* next_edge, const TcMlp* dec, int out
 int tc_enc_node(const TcMlp& m, const TcMlp& next_edge, int node_dim, const float* nodes, const TcGraph& g,
                 const TcBuffers& b, cudaStream_t stream) {
   GM_REQUIRE(node_dim >= 1 && node_dim <= kMaxIn1, "tc_enc_node: node_dim=%d outside [1,%d]", node_dim, kMaxIn1);
-  const size_t sm = smem_bytes(1);
+  const size_t sm = smem_bytes(2);
   int rc = tc_configure();
   if (rc) return rc;
   const int grid = min(ceil_div(g.n_nodes, kTile), kNumSMs);

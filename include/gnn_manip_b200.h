@@ -200,6 +200,10 @@ int gm_rollout_graph(const gm_rollout* plan, const int32_t** nbr, const int32_t*
 int64_t gm_rollout_kernel_launches_per_step(const gm_rollout* plan);
 void gm_rollout_destroy(gm_rollout* plan);
 
+/* Debug aid: phase timestamps (clock64) recorded by CTA 0 of the instrumented kernels; only in -DGM_STAMPS builds
+ * (returns GM_STATUS_UNSUPPORTED otherwise).  out_host: host array of n <= 64 values. */
+int gm_debug_stamps(unsigned long long* out_host, int32_t n);
+
 /* tcgen05 operand-path self test: out[M,128] = x[M,128] @ w[128,128]^T (bf16x3), M % 128 == 0.
  * chunk: 64 KB device scratch for the packed weight. */
 int gm_selftest_gemm(const float* x, const float* w, void* chunk, float* out, int32_t M, void* stream);

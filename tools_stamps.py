@@ -1,0 +1,17 @@
+"""Debug aid (needs a -DGM_STAMPS build: make -C gnn_manip_b200/csrc clean all EXTRA=-DGM_STAMPS):
+prints the phase timestamps CTA 0 recorded during one forward on the C2 or C3 scene."""
+import ctypes, sys
+import numpy as np, torch
+import gnn_manip_b200 as gm, scenes, bench
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 100_000
+torch.manual_seed(0)
+model = gm.EncProcDecGNN(25, 4, 3, 128, 2, 10)
+obs, _ = scenes.make_state(n, seed=0, n_rigid=0)
+per, E, N = bench.profile_forward(gm, model, obs, reps=2, warm=1, flush=None)
+st = (ctypes.c_ulonglong * 64)()
+gm._lib.check(gm._lib.lib().gm_debug_stamps(st, 64), "gm_debug_stamps")
+s = np.array(st[:], dtype=np.int64)
+print("kernel ms", per, "E", E)
+print("stamps (cycles since stamp 0):", [int(x - s[0]) for x in s[:24]])
+print("deltas:", [int(s[i + 1] - s[i]) for i in range(23)])
