@@ -748,6 +748,10 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
+#ifdef GM_STAMPS
+    const bool stamp_on = tile == (int)blockIdx.x;
+#endif
+    GM_STAMP(32);
     // ---- prologue: total aggregate per node (first-tile partial + carries of the following agg tiles) -> A0,
     //      node latents -> T (as the second layer-1 operand) ----
     {
@@ -786,10 +790,14 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
       load_rows_to_a16(c, T, rows_valid, [=](int r) { return v_in + (size_t)(node0 + r) * kH; });
     }
     // ---- layer 1: agg W1a^T + v W1b^T ----
+    GM_STAMP(33);
     launch_gemm(c, 0, 1, false);
+    GM_STAMP(34);
     wait_gemm(c, 0);
+    GM_STAMP(35);
     load_w(c, m.wc[1]);
-    launch_gemm(c, 1, 1, true);                    // sub 0 of launch_gemm(c, 1, ...) reads A buffer 1 (= T), TMEM cols 0
+    launch_gemm(c, 1, 1, true);
+    GM_STAMP(36);                    // sub 0 of launch_gemm(c, 1, ...) reads A buffer 1 (= T), TMEM cols 0
     wait_gemm(c, 0);
     load_w(c, m.wc[2]);
     {                                              // T is free: the fp32 residual rows travel into it meanwhile
@@ -798,18 +806,24 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
         return r < rows_valid ? v_in + (size_t)(node0 + r) * kH : nullptr;
       });
     }
+    GM_STAMP(37);
     epi_hidden_s(c, A0, prm + kPrmB1);
+    GM_STAMP(38);
     // ---- layer 2 ----
     launch_gemm(c, 0, 1, false);
+    GM_STAMP(39);
     wait_gemm(c, 0);
     load_w(c, m.wc[3]);
     epi_hidden_s(c, A0, prm + kPrmB2);
+    GM_STAMP(40);
     // ---- layer 3 + LayerNorm + residual, then the projections for the next edge step or the decoder ----
     cp_async_wait_all();
     launch_gemm(c, 0, 1, false);
     wait_gemm(c, 0);
     load_w(c, has_dec ? next.wc[0] : next.wc[3]);
+    GM_STAMP(41);
     node_finish(c, A0, T, prm, true, next, has_dec != 0, out_dim, pred, b, node0, rows_valid);
+    GM_STAMP(42);
     if (tile + (int)gridDim.x < n_tiles) load_w(c, m.wc[0]);
   }
   ctx_fini(c, 128);
@@ -875,68 +889,77 @@ enc_edge_kernel(TcMlp m, int edge_dim, const float* __restrict__ pos, int pos_st
                 const float* __restrict__ edge_attr, const int* __restrict__ eref, TcGraph g, TcBuffers b) {
   extern __shared__ char smem_raw[];
   Ctx c;
-  ctx_init(c, smem_raw, 1, 128);
+  ctx_init(c, smem_raw, 2, 128);
+  char* A0 = c.a[0];
+  char* T = c.a[1];
+  const float* prm = c.misc->prm;
+  stage_params(c, m);
   for (int i = c.tid; i < kH * edge_dim; i += NT) c.misc->w1[i] = m.w1[i];
-  for (int i = c.tid; i < kH; i += NT) c.misc->b1[i] = m.b1[i];
   __syncthreads();
   const int E = min(*g.n_edges_dev, g.max_edges);
   const int n_tiles = (E + kTile - 1) / kTile;
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int row0 = tile * kTile;
-    const int rows_valid = min(kTile, E - row0);
-    load_w(c, m.wc[2]);
-    float x[kMaxIn1];
+  // this thread's input row of a tile: explicit edge_attr row, or the displacement features built from positions
+  float xn[kMaxIn1];
+  auto load_x = [&](int t) {
 #pragma unroll
-    for (int k = 0; k < kMaxIn1; ++k) x[k] = 0.f;
-    if (c.row < rows_valid) {
-      const int ge = row0 + c.row;
+    for (int k = 0; k < kMaxIn1; ++k) xn[k] = 0.f;
+    const int ge = t * kTile + c.row;
+    if (ge < E) {
       if (edge_attr != nullptr) {
         const float* src = edge_attr + (size_t)(eref ? eref[ge] : ge) * edge_dim;
 #pragma unroll
         for (int k = 0; k < kMaxIn1; ++k)
-          if (k < edge_dim) x[k] = __ldg(src + k);
+          if (k < edge_dim) xn[k] = __ldg(src + k);
       } else {
         const float4 f = edge_feature(pos, pos_stride, g.esend[ge], g.erecv[ge], conn_r);
-        x[0] = f.x; x[1] = f.y; x[2] = f.z; x[3] = f.w;
+        xn[0] = f.x; xn[1] = f.y; xn[2] = f.z; xn[3] = f.w;
       }
     }
+  };
+  if ((int)blockIdx.x < n_tiles) {
+    load_w(c, m.wc[2]);
+    load_x(blockIdx.x);
+  }
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int row0 = tile * kTile;
+    const int rows_valid = min(kTile, E - row0);
+    const bool has_next = tile + (int)gridDim.x < n_tiles;
+    // layer 1 on CUDA cores: Linear(edge_dim, 128) + ReLU -> A0
 #pragma unroll 1
     for (int g8 = 0; g8 < 8; ++g8) {
       const int col0 = c.hf * 64 + g8 * 8;
       float h[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        float acc = c.misc->b1[col0 + j];
+        float acc = prm[kPrmB1 + col0 + j];
         const float* w = c.misc->w1 + (size_t)(col0 + j) * edge_dim;
 #pragma unroll
         for (int k = 0; k < kMaxIn1; ++k)
-          if (k < edge_dim) acc = fmaf(x[k], w[k], acc);
+          if (k < edge_dim) acc = fmaf(xn[k], w[k], acc);
         h[j] = fmaxf(acc, 0.f);
       }
-      store_a8(c.a[0], c.row, col0, h);
+      store_a8(A0, c.row, col0, h);
     }
     launch_gemm(c, 0, 1, false);
+    if (has_next) load_x(tile + gridDim.x);            // in flight during the GEMMs
     wait_gemm(c, 0);
     load_w(c, m.wc[3]);
-    epi_hidden(c, 0, 0, m.b2, nullptr, nullptr);
+    epi_hidden_s(c, A0, prm + kPrmB2);
     launch_gemm(c, 0, 1, false);
     wait_gemm(c, 0);
-    float mean, rstd;
-    ln_stats(c, 0, m.b3, mean, rstd);
-    const size_t grow = (size_t)(row0 + c.row) * kH;
-#pragma unroll 1
-    for (int hh = 0; hh < 2; ++hh) {
-      const int col0 = c.hf * 64 + hh * 32;
-      float v[32];
-      ln_apply32(c, 0, col0, m.b3, m.ln_g, m.ln_b, mean, rstd, v);
-      if (c.row < rows_valid) {
+    if (has_next) load_w(c, m.wc[2]);
+    {
+      float x[64];
+      ln_row64(c, prm, x);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          reinterpret_cast<float4*>(b.e + grow + col0)[j] =
-              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      }
+      for (int j = 0; j < 16; ++j)
+        *reinterpret_cast<float4*>(T + s_off(c.row, c.hf * 64 + 4 * j)) =
+            make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
     }
-    __syncthreads();   // all TMEM reads of this tile retire before the next tile's MMA overwrites D
+    tc_fence_before();
+    __syncthreads();
+    copy_out_rows(c, T, b.e, row0, rows_valid);
+    __syncthreads();                                   // T is rewritten by the next tile's LayerNorm epilogue
   }
   ctx_fini(c, 128);
 }
@@ -992,7 +1015,7 @@ int tc_configure() {
   if ((rc = set_smem(mp_edge_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(mp_node_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(enc_node_kernel, smem_bytes(2)))) return rc;
-  if ((rc = set_smem(enc_edge_kernel, smem_bytes(1)))) return rc;
+  if ((rc = set_smem(enc_edge_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(selftest_gemm_kernel, smem_bytes(1)))) return rc;
   done = true;
   return GM_OK;
@@ -1054,7 +1077,7 @@ int tc_enc_edge(const TcMlp& m, int edge_dim, const float* pos, int pos_stride, 
   GM_REQUIRE(edge_dim >= 1 && edge_dim <= kMaxIn1, "tc_enc_edge: edge_dim=%d outside [1,%d]", edge_dim, kMaxIn1);
   GM_REQUIRE(edge_attr != nullptr || edge_dim == 4, "tc_enc_edge: on-the-fly edge features need edge_dim == 4");
   if (g.max_edges <= 0) return GM_OK;
-  const size_t sm = smem_bytes(1);
+  const size_t sm = smem_bytes(2);
   int rc = tc_configure();
   if (rc) return rc;
   const int grid = min(ceil_div(g.max_edges, kTile), kNumSMs);

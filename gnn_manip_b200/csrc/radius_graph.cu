@@ -73,9 +73,7 @@ __global__ void bbox_kernel(const float* __restrict__ pos, int stride, int n, un
 }
 
 // One thread: choose the cell edge so that (cells per graph) * n_graphs fits the cell budget.
-__global__ void grid_setup_kernel(const unsigned* __restrict__ bbox, double r, int n_graphs, int max_cells,
-                                  GridParams* __restrict__ gp) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+__device__ void grid_setup_body(const unsigned* bbox, double r, int n_graphs, int max_cells, GridParams* gp) {
   double lo[3], ext[3];
   for (int d = 0; d < 3; ++d) {
     lo[d] = (double)ord2f(bbox[d]);
@@ -104,6 +102,54 @@ __global__ void grid_setup_kernel(const unsigned* __restrict__ bbox, double r, i
   }
   gp->cs = cs;
   gp->cells_per_graph = dim[0] * dim[1] * dim[2];
+}
+
+__global__ void grid_setup_kernel(const unsigned* __restrict__ bbox, double r, int n_graphs, int max_cells,
+                                  GridParams* __restrict__ gp) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  grid_setup_body(bbox, r, n_graphs, max_cells, gp);
+}
+
+// Small inputs (n <= kSmallN): one block computes the bounding box, sets the grid up and zeroes the counters
+// (replaces bbox_init + bbox + grid_setup + three memsets).
+constexpr int kSmallN = 1 << 15;
+__device__ void grid_setup_body(const unsigned* bbox, double r, int n_graphs, int max_cells, GridParams* gp);
+
+__global__ void __launch_bounds__(1024)
+prepare_small_kernel(const float* __restrict__ pos, int stride, int n, double r, int n_graphs, int max_cells,
+                     GridParams* __restrict__ gp, int* __restrict__ cell_cnt, int* __restrict__ indeg_fill /*2(n+1)*/) {
+  __shared__ unsigned s_box[6];
+  if (threadIdx.x < 3) s_box[threadIdx.x] = 0xFFFFFFFFu;
+  else if (threadIdx.x < 6) s_box[threadIdx.x] = 0u;
+  __syncthreads();
+  unsigned mn[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, mx[3] = {0u, 0u, 0u};
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const unsigned o = f2ord(pos[(size_t)i * stride + d]);
+      mn[d] = min(mn[d], o);
+      mx[d] = max(mx[d], o);
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[d] = min(mn[d], __shfl_xor_sync(0xffffffffu, mn[d], o));
+      mx[d] = max(mx[d], __shfl_xor_sync(0xffffffffu, mx[d], o));
+    }
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      atomicMin(&s_box[d], mn[d]);
+      atomicMax(&s_box[3 + d], mx[d]);
+    }
+  }
+  for (int i = threadIdx.x; i <= max_cells; i += blockDim.x) cell_cnt[i] = 0;
+  for (int i = threadIdx.x; i < 2 * (n + 1); i += blockDim.x) indeg_fill[i] = 0;
+  __syncthreads();
+  if (threadIdx.x == 0) grid_setup_body(s_box, r, n_graphs, max_cells, gp);
 }
 
 __device__ __forceinline__ void cell_coords(const GridParams& gp, float x, float y, float z, int c[3]) {
@@ -318,6 +364,57 @@ __global__ void recv_sort_emit_kernel(const int* __restrict__ recv_ptr, int n, i
   }
 }
 
+// Warp per receiver: every lane ranks its one or two keys against the whole segment with shuffles and
+// writes the sorted edge straight out (keys are distinct slot ids, so ranks are a permutation).
+__global__ void __launch_bounds__(256)
+recv_sort_emit_warp_kernel(const int* __restrict__ recv_ptr, int n, const int* __restrict__ keys, int K,
+                           const int* __restrict__ edge_ptr, const int* __restrict__ send_of_slot,
+                           int* __restrict__ esend, int* __restrict__ erecv, int* __restrict__ eref) {
+  const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (j >= n) return;
+  const int b = recv_ptr[j], len = recv_ptr[j + 1] - b;
+  const int k0 = lane < len ? keys[b + lane] : 0x7FFFFFFF;
+  const int k1 = lane + 32 < len ? keys[b + lane + 32] : 0x7FFFFFFF;
+  int r0 = 0, r1 = 0;
+#pragma unroll 8
+  for (int o = 0; o < 32; ++o) {
+    const int a0 = __shfl_sync(0xffffffffu, k0, o);
+    r0 += a0 < k0; r1 += a0 < k1;
+  }
+  if (len > 32) {
+#pragma unroll 8
+    for (int o = 0; o < 32; ++o) {
+      const int a1 = __shfl_sync(0xffffffffu, k1, o);
+      r0 += a1 < k0; r1 += a1 < k1;
+    }
+  }
+  auto emit = [&](int slot, int rank) {
+    int snd, ref;
+    if (K > 0) {
+      snd = slot / K;
+      ref = edge_ptr[snd] + (slot - snd * K);
+    } else {
+      snd = send_of_slot[slot];
+      ref = slot;
+    }
+    esend[b + rank] = snd;
+    erecv[b + rank] = j;
+    eref[b + rank] = ref;
+  };
+  if (len <= 64) {
+    if (lane < len) emit(k0, r0);
+    if (lane + 32 < len) emit(k1, r1);
+  } else {                                   // rare (the cap bounds out-degree, not in-degree): rank against global memory
+    for (int t = lane; t < len; t += 32) {
+      const int k = keys[b + t];
+      int rank = 0;
+      for (int u = 0; u < len; ++u) rank += keys[b + u] < k;
+      emit(k, rank);
+    }
+  }
+}
+
 __global__ void copy_last_kernel(const int* __restrict__ ptr, int n, int* __restrict__ out) {
   if (threadIdx.x == 0 && blockIdx.x == 0) *out = ptr[n];
 }
@@ -347,8 +444,8 @@ void radius_graph_carve(Arena& a, int n_total, int /*n_graphs*/, int K, RadiusGr
   ws.cell_cnt = a.take<int>((size_t)ws.max_cells + 1);
   ws.cell_start = a.take<int>((size_t)ws.max_cells + 2);
   ws.sorted = a.take<float4>(n_total);
-  ws.indeg = a.take<int>((size_t)n_total + 1);   // indeg and fill are contiguous: one memset
-  ws.fill = a.take<int>((size_t)n_total + 1);
+  ws.indeg = a.take<int>(2 * ((size_t)n_total + 1));   // indeg and fill are contiguous: zeroed together
+  ws.fill = ws.indeg + ((size_t)n_total + 1);
   ws.keys = a.take<int>((size_t)n_total * K);
   size_t scan_n = (size_t)ws.max_cells + 1 > (size_t)n_total + 1 ? (size_t)ws.max_cells + 1 : (size_t)n_total + 1;
   ws.scan_ws = a.take<int>(scan_workspace_ints((long long)scan_n) + 8);
@@ -356,7 +453,8 @@ void radius_graph_carve(Arena& a, int n_total, int /*n_graphs*/, int K, RadiusGr
 
 int build_recv_csr(const int* recv_of_slot, long long n_slots, const int* n_valid_dev, int n_nodes, int K,
                    const int* edge_ptr, const int* send_of_slot, int* indeg, int* fill, int* keys, int* scan_ws,
-                   bool indeg_ready, int* recv_ptr, int* esend, int* erecv, int* eref, cudaStream_t stream) {
+                   bool indeg_ready, int* recv_ptr, int* esend, int* erecv, int* eref, cudaStream_t stream,
+                   bool fill_ready) {
   const int T = 256;
   if (!indeg_ready) {
     GM_CUDA(cudaMemsetAsync(indeg, 0, sizeof(int) * ((size_t)n_nodes + 1), stream));
@@ -365,7 +463,7 @@ int build_recv_csr(const int* recv_of_slot, long long n_slots, const int* n_vali
       GM_LAUNCHED(1);
     }
   }
-  GM_CUDA(cudaMemsetAsync(fill, 0, sizeof(int) * ((size_t)n_nodes + 1), stream));
+  if (!fill_ready) GM_CUDA(cudaMemsetAsync(fill, 0, sizeof(int) * ((size_t)n_nodes + 1), stream));
   int rc = exclusive_scan_i32(indeg, recv_ptr, n_nodes, scan_ws, stream);
   if (rc) return rc;
   if (n_slots > 0) {
@@ -373,8 +471,8 @@ int build_recv_csr(const int* recv_of_slot, long long n_slots, const int* n_vali
     GM_LAUNCHED(1);
   }
   if (n_nodes > 0) {
-    recv_sort_emit_kernel<<<ceil_div(n_nodes, 128), 128, 0, stream>>>(recv_ptr, n_nodes, keys, K, edge_ptr,
-                                                                     send_of_slot, esend, erecv, eref);
+    recv_sort_emit_warp_kernel<<<ceil_div(n_nodes, 8), 256, 0, stream>>>(recv_ptr, n_nodes, keys, K, edge_ptr,
+                                                                        send_of_slot, esend, erecv, eref);
     GM_LAUNCHED(1);
   }
   GM_LAUNCH_CHECK("build_recv_csr");
@@ -394,11 +492,18 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
   const int T = 256;
   GridParams* gp = reinterpret_cast<GridParams*>(ws.grid);
 
-  bbox_init_kernel<<<1, 32, 0, stream>>>(ws.bbox);
-  bbox_kernel<<<min(ceil_div(n, T), 4 * kNumSMs), T, 0, stream>>>(pos, pos_stride, n, ws.bbox);
-  grid_setup_kernel<<<1, 32, 0, stream>>>(ws.bbox, r, n_graphs, ws.max_cells, gp);
-  GM_CUDA(cudaMemsetAsync(ws.cell_cnt, 0, sizeof(int) * ((size_t)ws.max_cells + 1), stream));
-  GM_CUDA(cudaMemsetAsync(ws.indeg, 0, sizeof(int) * ((size_t)n + 1), stream));
+  const bool small = n <= kSmallN;
+  if (small) {
+    prepare_small_kernel<<<1, 1024, 0, stream>>>(pos, pos_stride, n, r, n_graphs, ws.max_cells, gp, ws.cell_cnt, ws.indeg);
+    GM_LAUNCHED(1);
+  } else {
+    bbox_init_kernel<<<1, 32, 0, stream>>>(ws.bbox);
+    bbox_kernel<<<min(ceil_div(n, T), 4 * kNumSMs), T, 0, stream>>>(pos, pos_stride, n, ws.bbox);
+    grid_setup_kernel<<<1, 32, 0, stream>>>(ws.bbox, r, n_graphs, ws.max_cells, gp);
+    GM_CUDA(cudaMemsetAsync(ws.cell_cnt, 0, sizeof(int) * ((size_t)ws.max_cells + 1), stream));
+    GM_CUDA(cudaMemsetAsync(ws.indeg, 0, sizeof(int) * ((size_t)n + 1), stream));
+    GM_LAUNCHED(3);
+  }
   cell_count_kernel<<<ceil_div(n, T), T, 0, stream>>>(pos, pos_stride, n, n_per_graph, gp, ws.cell_of, ws.cell_cnt);
   int rc = exclusive_scan_i32(ws.cell_cnt, ws.cell_start, ws.max_cells, ws.scan_ws, stream);
   if (rc) return rc;
@@ -406,17 +511,12 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
                                                      ws.sorted);
   neighbour_kernel<<<ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream>>>(
       ws.sorted, ws.cell_start, gp, n, n_per_graph, r * r, K, nbr, cnt, ws.indeg);
-  GM_LAUNCHED(6);
+  GM_LAUNCHED(3);
   GM_LAUNCH_CHECK("radius_graph kernels");
-  rc = exclusive_scan_i32(cnt, edge_ptr, n, ws.scan_ws, stream);
+  rc = exclusive_scan_i32(cnt, edge_ptr, n, ws.scan_ws, stream, n_edges);
   if (rc) return rc;
-  rc = build_recv_csr(nbr, (long long)n * K, nullptr, n, K, edge_ptr, nullptr, ws.indeg, ws.fill, ws.keys,
-                      ws.scan_ws, /*indeg_ready=*/true, recv_ptr, esend, erecv, eref, stream);
-  if (rc) return rc;
-  copy_last_kernel<<<1, 32, 0, stream>>>(edge_ptr, n, n_edges);
-  GM_LAUNCHED(1);
-  GM_LAUNCH_CHECK("radius_graph tail");
-  return GM_OK;
+  return build_recv_csr(nbr, (long long)n * K, nullptr, n, K, edge_ptr, nullptr, ws.indeg, ws.fill, ws.keys,
+                        ws.scan_ws, /*indeg_ready=*/true, recv_ptr, esend, erecv, eref, stream, /*fill_ready=*/small);
 }
 
 }  // namespace gm

@@ -99,15 +99,63 @@ static __global__ void scan_apply_kernel(const int* __restrict__ in, long long n
   if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = block_sums[nblocks];
 }
 
+// Small inputs: one block walks the array tile by tile (one launch instead of three).
+constexpr long long kScanSingleBlockMax = 1 << 14;
+static __global__ void scan_single_block_kernel(const int* __restrict__ in, long long n, int* __restrict__ out,
+                                                int* __restrict__ total_out) {
+  __shared__ int sm[9];
+  int carry = 0;
+  for (long long base0 = 0; base0 < n; base0 += kScanTile) {
+    const long long base = base0 + (long long)threadIdx.x * kScanItems;
+    int v[kScanItems];
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      const long long k = base + i;
+      v[i] = k < n ? in[k] : 0;
+      s += v[i];
+    }
+    int total;
+    int ex = block_exclusive_scan_256(s, &total, sm) + carry;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      const long long k = base + i;
+      if (k < n) out[k] = ex;
+      ex += v[i];
+    }
+    carry += total;
+  }
+  if (threadIdx.x == 0) {
+    out[n] = carry;
+    if (total_out) *total_out = carry;
+  }
+}
+
+static __global__ void scan_copy_total_kernel(const int* __restrict__ out, long long n, int* __restrict__ total_out) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *total_out = out[n];
+}
+
 // out has n+1 entries; `ws` has scan_workspace_ints(n) ints. in/out may alias only if identical pointers are
 // NOT used (phase C reads `in` after phase A; aliasing in==out is safe because each block reads its own
 // items before writing them and never reads another block's items).
-inline int exclusive_scan_i32(const int* in, int* out, long long n, int* ws, cudaStream_t stream) {
+// total_out (optional, device): receives the grand total as well.
+inline int exclusive_scan_i32(const int* in, int* out, long long n, int* ws, cudaStream_t stream,
+                              int* total_out = nullptr) {
+  if (n <= kScanSingleBlockMax) {
+    scan_single_block_kernel<<<1, kScanThreads, 0, stream>>>(in, n, out, total_out);
+    GM_LAUNCHED(1);
+    GM_LAUNCH_CHECK("scan_single_block_kernel");
+    return GM_OK;
+  }
   const int nb = scan_num_blocks(n);
   scan_block_sums_kernel<<<nb, kScanThreads, 0, stream>>>(in, n, ws);
   scan_block_offsets_kernel<<<1, kScanThreads, 0, stream>>>(ws, nb);
   scan_apply_kernel<<<nb, kScanThreads, 0, stream>>>(in, n, ws, nb, out);
   GM_LAUNCHED(3);
+  if (total_out) {
+    scan_copy_total_kernel<<<1, 32, 0, stream>>>(out, n, total_out);
+    GM_LAUNCHED(1);
+  }
   GM_LAUNCH_CHECK("exclusive_scan_i32");
   return GM_OK;
 }

@@ -15,3 +15,4 @@ s = np.array(st[:], dtype=np.int64)
 print("kernel ms", per, "E", E)
 print("stamps (cycles since stamp 0):", [int(x - s[0]) for x in s[:24]])
 print("deltas:", [int(s[i + 1] - s[i]) for i in range(23)])
+print("node stamps:", [int(x - s[32]) for x in s[32:44]])
