@@ -83,6 +83,7 @@ SIGNATURES = {
     "gm_rollout_destroy": (None, [c_void_p]),
     "gm_debug_stamps": (ctypes.c_int, [c_void_p, c_int32]),
     "gm_selftest_gemm": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),
+    "gm_selftest_gemm_ts": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),
 }
 
 _lib = None

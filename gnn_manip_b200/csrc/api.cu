@@ -803,4 +803,10 @@ int gm_selftest_gemm(const float* x, const float* w, void* chunk, float* out, in
   return tc_selftest_gemm(x, chunk, out, M, (cudaStream_t)stream);
 }
 
+int gm_selftest_gemm_ts(const float* x, const float* w, void* chunk, float* out, int32_t M, void* stream) {
+  int rc = tc_pack_chunk(w, kH, 0, chunk, (cudaStream_t)stream);
+  if (rc) return rc;
+  return tc_selftest_gemm_ts(x, chunk, out, M, (cudaStream_t)stream);
+}
+
 }  // extern "C"

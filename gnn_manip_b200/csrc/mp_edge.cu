@@ -1,0 +1,643 @@
+// Row A3 (+ the scatter_add of A4) -- edge half of one message-passing step, warp-specialised and software-pipelined.
+//
+// Replaces EdgeModel.forward (deps/torch-graphnet/torch_graphnet/graph_networks.py:29-50), the residual of
+// EncProcDecGNN._process (gnn_manip/models/epd_gnn.py:104) and scatter_sum (utils/gn_utils.py:60-64).
+//
+// One persistent CTA per SM, 320 threads:
+//   warps 0-3  compute warpgroup of tile slot 0   } thread = one edge row of a 128-edge tile: operand split,
+//   warps 4-7  compute warpgroup of tile slot 1   } bias/ReLU/LayerNorm epilogues, segmented receiver sum
+//   warp  8    tcgen05.mma issuer (one thread)
+//   warp  9    weight producer (one thread, cp.async.bulk through the TMA unit)
+// Two 128-edge tiles are in flight per SM; while one tile's accumulator is in an epilogue the tensor core works on
+// the other tile (G_l(slot 0), G_l(slot 1), G_l+1(slot 0), ...), so both tiles share every weight piece.
+//
+// Memory plan
+//   TMEM (512 columns): per slot 128 fp32 accumulator columns + the A operand of the next GEMM as bf16 hi / lo
+//     images (64 + 64 columns, lane = edge row, two K elements per 32-bit column).  Epilogues write the next A
+//     operand straight into TMEM with tcgen05.st -- no swizzled shared-memory operand, no st.shared bandwidth --
+//     and the MMAs read A from TMEM and only the weights from shared memory.
+//   SMEM: ring of 16 KB weight pieces {Wh.k0, Wh.k1, Wl.k0, Wl.k1} per layer, refilled piece by piece as soon as
+//     the second tile has consumed one; one 64 KB fp32 staging tile per slot, stored as four 32-column boxes of
+//     128 x 128 B with the 16-byte chunk index XOR (row & 7): conflict-free for row-owner 128-bit access and for
+//     column-owner 32-bit access.  Each warp stages exactly the 32 rows its own threads own (cp.async, one
+//     coalesced 512 B row per instruction: e rows in, then the Ps[send] gather), so those hand-offs are
+//     warp-local; LayerNorm rows leave as vector reductions into e (red.global.add.v4.f32: e' = e + LN(...), the
+//     residual is added in L2 and the fp32 residual never enters the SM a second time).
+//   bf16x3: x.w ~= xh.wh + xl.wh + xh.wl, accumulated in fp32 in TMEM.
+#include "mp_tc.cuh"
+
+namespace gm {
+
+namespace {
+
+constexpr int kNTE = 320;
+constexpr int kPieceBytes = 16384;           // one K block (64 columns) of one 128-row bf16 image
+constexpr int kRing = 5;                     // weight pieces resident
+constexpr int kBoxBytes = kTile * 128;       // one 32-column box of the staging tile
+constexpr int kStageBytes = 4 * kBoxBytes;   // 64 KB
+constexpr uint32_t kIdescE = umma_idesc_bf16(kTile, kH);
+
+struct EdgeShared {
+  uint64_t w_full[kRing];
+  uint64_t w_free[kRing];
+  uint64_t a_ready[2];                       // operand of the next GEMM is in TMEM (4 warp arrivals)
+  uint64_t d_ready[2];                       // accumulator complete (tcgen05.commit)
+  uint32_t tmem_base;
+  uint32_t pad;
+  uint32_t segmask[2][4];                    // bit l of word q: row 32q+l starts a new receiver segment
+  alignas(16) float prm[4 * kH];             // b2 | b3 | LayerNorm gamma | LayerNorm beta
+};
+constexpr int kEdgeSmemBytes = kRing * kPieceBytes + 2 * kStageBytes + (int)sizeof(EdgeShared) + 1024;
+static_assert(kEdgeSmemBytes <= 232448, "mp_edge shared memory exceeds 227 KB");
+
+// Staging tile addressing.  Element (row, col): box col >> 5, then row * 128 + ((chunk ^ (row & 7)) << 4) + (col & 3) * 4
+// with chunk = (col >> 2) & 7.
+//   row owner (thread = row): float4 j of the row sits at  box(j >> 3) + rowoff[j & 7]
+//   stager    (warp per row): lane l moves float4 l of the row
+__device__ __forceinline__ uint32_t stage_chunk_off(int row, int j) {
+  return (uint32_t)(j >> 3) * kBoxBytes + (uint32_t)row * 128u + ((((uint32_t)j & 7u) ^ ((uint32_t)row & 7u)) << 4);
+}
+
+// Warp-per-row staging of this warp's 32 rows [r0, r0 + 32) (r0 % 8 == 0), one coalesced 512 B row per cp.async
+// instruction.  db[ii]: destination of this lane's float4 in row r0 + ii (ii < 8); row r0 + i sits at db[i & 7] +
+// (i & ~7) * 128.  n_valid rows are copied, the rest zero-filled.
+__device__ __forceinline__ void stage_dst_init(uint32_t S_s, int r0, int lane, uint32_t* db) {
+#pragma unroll
+  for (int ii = 0; ii < 8; ++ii) db[ii] = S_s + stage_chunk_off(r0 + ii, lane);
+}
+// contiguous source rows (src0 = this lane's float4 of row r0)
+__device__ __forceinline__ void stage_rows32_contig(const uint32_t* db, const float* src0, int n_valid) {
+  if (n_valid >= 32) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) cp_async16(db[i & 7] + (i & ~7) * 128, src0 + i * kH, 16u);
+  } else {
+#pragma unroll 8
+    for (int i = 0; i < 32; ++i) cp_async16(db[i & 7] + (i & ~7) * 128, i < n_valid ? src0 + i * kH : src0, i < n_valid ? 16u : 0u);
+  }
+  cp_async_commit();
+}
+// gathered source rows: lane i of the warp holds the source row index of row r0 + i (< 0: zero fill)
+__device__ __forceinline__ void stage_rows32_gather(const uint32_t* db, const float* table_lane, int my_idx) {
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    const int sid = __shfl_sync(0xffffffffu, my_idx, i);
+    cp_async16(db[i & 7] + (i & ~7) * 128, table_lane + (size_t)(sid < 0 ? 0 : sid) * kH, sid < 0 ? 0u : 16u);
+  }
+  cp_async_commit();
+}
+
+__device__ __forceinline__ void red_add_v4(float* gdst, const float4& v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(gdst), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// 32 lanes x 16 columns: thread i of the warp writes TMEM lane (base_lane + i), columns [col, col + 16)
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// D[tmem_d] (+)= A[tmem_a] x B[smem]^T, A from tensor memory (lane = row, 8 columns = 16 bf16 along K)
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      :
+      : "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// one GEMM piece: p = 0/1 -> Wh K-block p against A hi and A lo; p = 2/3 -> Wl K-block p-2 against A hi
+__device__ __forceinline__ void issue_piece(int p, uint32_t w_piece_s, uint32_t tD, uint32_t tAH, uint32_t tAL) {
+  const uint32_t kcol = (uint32_t)(p & 1) * 32u;
+#pragma unroll
+  for (int ks = 0; ks < 4; ++ks)
+    umma_bf16_ts(tD, tAH + kcol + ks * 8, umma_desc_sw128(w_piece_s + ks * 32), kIdescE, (p | ks) ? 1u : 0u);
+  if (p < 2) {
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks)
+      umma_bf16_ts(tD, tAL + kcol + ks * 8, umma_desc_sw128(w_piece_s + ks * 32), kIdescE, 1u);
+  }
+}
+
+// 32 fp32 values -> bf16 hi / lo pairs -> 16 + 16 TMEM columns of the A operand
+__device__ __forceinline__ void put_operand32(const float* v, uint32_t tAH, uint32_t tAL, int c32) {
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) split_bf16x2(v[2 * j], v[2 * j + 1], hi[j], lo[j]);
+  tmem_st16(tAH + c32 * 16, hi);
+  tmem_st16(tAL + c32 * 16, lo);
+}
+
+// this thread's staged fp32 row -> A operand (hi / lo) in TMEM.  S: staging tile, ro[jj]: row-owner chunk offsets
+__device__ __forceinline__ void row_to_operand(const char* S, const uint32_t* ro, uint32_t tAH, uint32_t tAL) {
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 t = *reinterpret_cast<const float4*>(S + c * kBoxBytes + ro[j]);
+      v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+    }
+    put_operand32(v, tAH, tAL, c);
+  }
+}
+
+__device__ __forceinline__ void publish_operand(uint32_t bar_a, int lane) {
+  tmem_st_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar_a);
+}
+
+// Phase timestamps (debug aid, -DGM_STAMPS): thread 0 of CTA 0 (slot 0) records clock64() during its third tile,
+// the MMA issuer during the matching pair; read back with gm_debug_stamps() (entries 0..31).
+#ifdef GM_STAMPS
+__device__ unsigned long long g_edge_stamps[32];
+#define GM_ESTAMP(i) do { if (stamp_on) g_edge_stamps[i] = clock64(); } while (0)
+#else
+#define GM_ESTAMP(i) do { } while (0)
+#endif
+
+constexpr int kOffB2 = 0, kOffB3 = 128, kOffG = 256, kOffBeta = 384;
+
+}  // namespace
+
+__global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, TcBuffers b) {
+  extern __shared__ char smem_raw[];
+  char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const uint32_t W_s = smem_u32(base);
+  char* S_base = base + kRing * kPieceBytes;
+  EdgeShared* sh = reinterpret_cast<EdgeShared*>(S_base + 2 * kStageBytes);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    for (int i = 0; i < kRing; ++i) {
+      mbar_init(smem_u32(&sh->w_full[i]), 1);
+      mbar_init(smem_u32(&sh->w_free[i]), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(smem_u32(&sh->a_ready[s]), 4);
+      mbar_init(smem_u32(&sh->d_ready[s]), 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 8) {
+    tmem_alloc(smem_u32(&sh->tmem_base), 512);
+    tmem_relinquish();
+  }
+  for (int i = tid; i < kH; i += kNTE) {
+    sh->prm[kOffB2 + i] = m.b2[i];
+    sh->prm[kOffB3 + i] = m.b3[i];
+    sh->prm[kOffG + i] = m.ln_g[i];
+    sh->prm[kOffBeta + i] = m.ln_b[i];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sh->tmem_base;
+
+  const int E = min(*g.n_edges_dev, g.max_edges);
+  const int n_tiles = (E + kTile - 1) / kTile;
+  const int grid = (int)gridDim.x;
+  const int n_my = (int)blockIdx.x < n_tiles ? (n_tiles - (int)blockIdx.x + grid - 1) / grid : 0;
+  const int n_pairs = (n_my + 1) >> 1;
+
+  if (warp == 9) {
+    // ---------------- weight producer ----------------
+    if (lane == 0) {
+      int n = 0;
+      for (int j = 0; j < n_pairs; ++j)
+        for (int l = 0; l < 3; ++l)
+          for (int p = 0; p < 4; ++p, ++n) {
+            const int slot = n % kRing;
+            if (n >= kRing) mbar_wait(smem_u32(&sh->w_free[slot]), (uint32_t)((n / kRing) - 1) & 1u);
+            const uint32_t bar = smem_u32(&sh->w_full[slot]);
+            mbar_expect_tx(bar, kPieceBytes);
+            bulk_g2s(W_s + slot * kPieceBytes, (const char*)m.wc[l] + (size_t)p * kPieceBytes, kPieceBytes, bar);
+          }
+    }
+    __syncwarp();
+  } else if (warp == 8) {
+    // ---------------- MMA issuer ----------------
+    if (lane == 0) {
+      uint32_t pa[2] = {0u, 0u};
+      int n = 0;
+      for (int j = 0; j < n_pairs; ++j) {
+        const int nt = min(2, n_my - 2 * j);
+        for (int l = 0; l < 3; ++l) {
+          for (int s = 0; s < nt; ++s) {
+#ifdef GM_STAMPS
+            const bool stamp_on = blockIdx.x == 0 && j == 2;
+#endif
+            GM_ESTAMP(16 + (l * 2 + s) * 2);
+            mbar_wait(smem_u32(&sh->a_ready[s]), pa[s]);
+            pa[s] ^= 1u;
+            tc_fence_after();
+            GM_ESTAMP(17 + (l * 2 + s) * 2);
+            const uint32_t tD = tmem + 256u * s, tAH = tD + 128u, tAL = tD + 192u;
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+              const int idx = n + p, slot = idx % kRing;
+              mbar_wait(smem_u32(&sh->w_full[slot]), (uint32_t)(idx / kRing) & 1u);
+              issue_piece(p, W_s + slot * kPieceBytes, tD, tAH, tAL);
+              if (s == nt - 1) umma_commit(smem_u32(&sh->w_free[slot]));
+            }
+            umma_commit(smem_u32(&sh->d_ready[s]));
+          }
+          n += 4;
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---------------- compute warpgroups: slot s, thread = edge row r ----------------
+    const int s = warp >> 2, q = warp & 3, r = tid & (kTile - 1), r0 = q * 32;
+    char* S = S_base + s * kStageBytes;
+    const uint32_t S_s = smem_u32(S);
+    uint32_t ro[8];                            // row-owner offsets of the 8 chunks of a box
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ro[j] = stage_chunk_off(r, j);
+    const uint32_t tD = tmem + ((uint32_t)r0 << 16) + 256u * s, tAH = tD + 128u, tAL = tD + 192u;
+    const uint32_t bar_a = smem_u32(&sh->a_ready[s]), bar_d = smem_u32(&sh->d_ready[s]);
+    const float* prm = sh->prm;
+    uint32_t ph_d = 0;
+
+    int nx_recv = -1, nx_send = -1, nx_prev = -2;
+    auto fetch_ids = [&](int k) {
+      const int ge = (blockIdx.x + k * grid) * kTile + r;
+      nx_recv = nx_send = -1;
+      nx_prev = -2;
+      if (ge < E) {
+        nx_recv = __ldg(g.erecv + ge);
+        nx_send = __ldg(g.esend + ge);
+        if (ge > 0) nx_prev = __ldg(g.erecv + ge - 1);
+      }
+    };
+    uint32_t db[8];                            // stager destinations of this lane
+    stage_dst_init(S_s, r0, lane, db);
+    auto stage_e_rows = [&](int k) {           // this warp's 32 rows of tile k
+      const int ge0 = (blockIdx.x + k * grid) * kTile + r0;
+      stage_rows32_contig(db, b.e + (size_t)ge0 * kH + 4 * lane, E - ge0);
+    };
+    if (s < n_my) {
+      fetch_ids(s);
+      stage_e_rows(s);
+    }
+    for (int k = s; k < n_my; k += 2) {
+      const int row0 = (blockIdx.x + k * grid) * kTile;
+      const int rows_valid = min(kTile, E - row0);
+      const bool live = r < rows_valid;
+      const int my_recv = nx_recv, my_send = nx_send, my_prev = nx_prev;
+#ifdef GM_STAMPS
+      const bool stamp_on = blockIdx.x == 0 && tid == 0 && k == 4;
+#endif
+      GM_ESTAMP(0);
+      if (k + 2 < n_my) {
+        fetch_ids(k + 2);
+        // pull the e rows of the tile after next towards L2: lane -> (row r0 + 8 i + lane / 4, 128 B line lane % 4)
+        const int ge0 = (blockIdx.x + (k + 2) * grid) * kTile + r0 + (lane >> 2);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (ge0 + 8 * i < E) prefetch_l2(b.e + (size_t)(ge0 + 8 * i) * kH + (lane & 3) * 32);
+      }
+      {
+        const unsigned mk = __ballot_sync(0xffffffffu, my_recv != my_prev);
+        if (lane == 0) sh->segmask[s][q] = mk;
+      }
+      const float* pr_row = b.pr + (size_t)(live ? my_recv : 0) * kH;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) prefetch_l1(pr_row + 32 * i);
+      // ---- operand of layer 1: e rows -> bf16 hi / lo in TMEM; then the Ps[send] gather reuses the staging rows ----
+      cp_async_wait_all();
+      __syncwarp();
+      GM_ESTAMP(1);
+      row_to_operand(S, ro, tAH, tAL);
+      tmem_st_wait();
+      __syncwarp();                            // every lane is done reading this warp's rows
+      GM_ESTAMP(2);
+      stage_rows32_gather(db, b.ps + 4 * lane, my_send);
+      publish_operand(bar_a, lane);
+      GM_ESTAMP(3);
+      // ---- layer 1 epilogue: relu(D + Pr[recv] (b1 folded in) + Ps[send]) ----
+      cp_async_wait_all();
+      __syncwarp();
+      GM_ESTAMP(4);
+      mbar_wait(bar_d, ph_d);
+      ph_d ^= 1u;
+      tc_fence_after();
+      GM_ESTAMP(5);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float v[32];
+        tmem_ld32(tD + c * 32, v);
+        float4 p[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) p[j] = __ldg(reinterpret_cast<const float4*>(pr_row + c * 32) + j);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 s4 = *reinterpret_cast<const float4*>(S + c * kBoxBytes + ro[j]);
+          v[4 * j] = fmaxf(v[4 * j] + (p[j].x + s4.x), 0.f);
+          v[4 * j + 1] = fmaxf(v[4 * j + 1] + (p[j].y + s4.y), 0.f);
+          v[4 * j + 2] = fmaxf(v[4 * j + 2] + (p[j].z + s4.z), 0.f);
+          v[4 * j + 3] = fmaxf(v[4 * j + 3] + (p[j].w + s4.w), 0.f);
+        }
+        put_operand32(v, tAH, tAL, c);
+      }
+      publish_operand(bar_a, lane);
+      GM_ESTAMP(6);
+      // ---- layer 2 epilogue: relu(D + b2) ----
+      mbar_wait(bar_d, ph_d);
+      ph_d ^= 1u;
+      tc_fence_after();
+      GM_ESTAMP(7);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float v[32];
+        tmem_ld32(tD + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 bs = *reinterpret_cast<const float4*>(prm + kOffB2 + c * 32 + 4 * j);
+          v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f);
+          v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
+          v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f);
+          v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w, 0.f);
+        }
+        put_operand32(v, tAH, tAL, c);
+      }
+      publish_operand(bar_a, lane);
+      GM_ESTAMP(8);
+      // ---- layer 3 epilogue: y = LayerNorm(D + b3) -> staging row (two sweeps over the accumulator in TMEM) ----
+      mbar_wait(bar_d, ph_d);
+      ph_d ^= 1u;
+      tc_fence_after();
+      GM_ESTAMP(9);
+      {
+        float sa = 0.f, sb = 0.f, qa = 0.f, qb = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          float v[32];
+          tmem_ld32(tD + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 t = *reinterpret_cast<const float4*>(prm + kOffB3 + c * 32 + 4 * j);
+            const float x0 = v[4 * j] + t.x, x1 = v[4 * j + 1] + t.y, x2 = v[4 * j + 2] + t.z, x3 = v[4 * j + 3] + t.w;
+            sa += x0; sb += x1; sa += x2; sb += x3;
+            qa = fmaf(x0, x0, qa); qb = fmaf(x1, x1, qb); qa = fmaf(x2, x2, qa); qb = fmaf(x3, x3, qb);
+          }
+        }
+        const float mean = (sa + sb) * (1.0f / kH);
+        const float var = fmaxf((qa + qb) * (1.0f / kH) - mean * mean, 0.f);
+        const float rstd = 1.0f / sqrtf(var + 1e-5f);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          float v[32];
+          tmem_ld32(tD + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 t = *reinterpret_cast<const float4*>(prm + kOffB3 + c * 32 + 4 * j);
+            const float4 g4 = *reinterpret_cast<const float4*>(prm + kOffG + c * 32 + 4 * j);
+            const float4 b4 = *reinterpret_cast<const float4*>(prm + kOffBeta + c * 32 + 4 * j);
+            *reinterpret_cast<float4*>(S + c * kBoxBytes + ro[j]) =
+                make_float4(((v[4 * j] + t.x) - mean) * rstd * g4.x + b4.x,
+                            ((v[4 * j + 1] + t.y) - mean) * rstd * g4.y + b4.y,
+                            ((v[4 * j + 2] + t.z) - mean) * rstd * g4.z + b4.z,
+                            ((v[4 * j + 3] + t.w) - mean) * rstd * g4.w + b4.w);
+          }
+        }
+      }
+      __syncwarp();
+      GM_ESTAMP(10);
+      // ---- e' = e + y (epd_gnn.py:104): this warp's rows leave as 512 B vector reductions, the add happens in L2 ----
+      {
+        const int nr = min(32, rows_valid - r0);
+        float* e_out = b.e + (size_t)(row0 + r0) * kH + 4 * lane;
+        if (nr >= 32) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            red_add_v4(e_out + i * kH, *reinterpret_cast<const float4*>(S + (db[i & 7] - S_s) + (i & ~7) * 128));
+        } else {
+#pragma unroll 8
+          for (int i = 0; i < 32; ++i)
+            if (i < nr) red_add_v4(e_out + i * kH, *reinterpret_cast<const float4*>(S + (db[i & 7] - S_s) + (i & ~7) * 128));
+        }
+      }
+      named_bar_sync(1 + s, kTile);
+      GM_ESTAMP(11);
+      // ---- receiver-segmented sum of the pre-residual rows: thread = column r, two 64-row halves interleaved,
+      //      8 + 8 rows loaded per step; segment starts come from the bit masks, so control flow is uniform ----
+      {
+        const uint32_t cbase = (uint32_t)(r >> 5) * kBoxBytes + ((uint32_t)r & 3u) * 4u;
+        const uint32_t cchunk = ((uint32_t)r >> 2) & 7u;
+        uint32_t co[8];
+#pragma unroll
+        for (int ii = 0; ii < 8; ++ii) co[ii] = cbase + ((cchunk ^ (uint32_t)ii) << 4);
+        const int n0 = min(kAggRows, rows_valid), n1 = max(0, min(kAggRows, rows_valid - kAggRows));
+        const unsigned long long m0 = (((unsigned long long)sh->segmask[s][1] << 32) | sh->segmask[s][0]) & ~1ull;
+        const unsigned long long m1 = (((unsigned long long)sh->segmask[s][3] << 32) | sh->segmask[s][2]) & ~1ull;
+        const size_t t0 = (size_t)row0 / kAggRows;
+        const int* erecv_t = g.erecv + row0;
+        float a0 = 0.f, a1 = 0.f;
+        bool c0 = !(sh->segmask[s][0] & 1u), c1 = !(sh->segmask[s][2] & 1u);   // row continues the previous agg tile
+        // receiver id of the running segment, fetched when the segment starts (used one segment later)
+        int id0 = n0 > 0 ? __ldg(erecv_t) : 0, id1 = n1 > 0 ? __ldg(erecv_t + kAggRows) : 0;
+        auto flush = [&](float acc, bool cont, int rid, size_t agg_tile) {
+          if (cont) b.carry[agg_tile * kH + r] = acc;
+          else b.aggpart[(size_t)rid * kH + r] = acc;
+        };
+#pragma unroll 1
+        for (int bb = 0; bb < kAggRows / 8; ++bb) {
+          float y0[8], y1[8];
+          const char* p = S + bb * 1024;
+#pragma unroll
+          for (int ii = 0; ii < 8; ++ii) {
+            y0[ii] = *reinterpret_cast<const float*>(p + co[ii] + ii * 128);
+            y1[ii] = *reinterpret_cast<const float*>(p + kAggRows * 128 + co[ii] + ii * 128);
+          }
+          const unsigned mb0 = (unsigned)(m0 >> (8 * bb)) & 0xffu, mb1 = (unsigned)(m1 >> (8 * bb)) & 0xffu;
+          const int nb0 = n0 - 8 * bb, nb1 = n1 - 8 * bb;
+          if (mb0 == 0u && nb0 >= 8) {
+#pragma unroll
+            for (int ii = 0; ii < 8; ++ii) a0 += y0[ii];
+          } else {
+#pragma unroll
+            for (int ii = 0; ii < 8; ++ii) {
+              if (ii < nb0) {
+                if ((mb0 >> ii) & 1u) {
+                  flush(a0, c0, id0, t0);
+                  a0 = 0.f; c0 = false; id0 = __ldg(erecv_t + 8 * bb + ii);
+                }
+                a0 += y0[ii];
+              }
+            }
+          }
+          if (mb1 == 0u && nb1 >= 8) {
+#pragma unroll
+            for (int ii = 0; ii < 8; ++ii) a1 += y1[ii];
+          } else {
+#pragma unroll
+            for (int ii = 0; ii < 8; ++ii) {
+              if (ii < nb1) {
+                if ((mb1 >> ii) & 1u) {
+                  flush(a1, c1, id1, t0 + 1);
+                  a1 = 0.f; c1 = false; id1 = __ldg(erecv_t + kAggRows + 8 * bb + ii);
+                }
+                a1 += y1[ii];
+              }
+            }
+          }
+        }
+        if (n0 > 0) flush(a0, c0, id0, t0);
+        if (n1 > 0) flush(a1, c1, id1, t0 + 1);
+      }
+      GM_ESTAMP(12);
+      named_bar_sync(1 + s, kTile);            // every row has been read: the slot's staging tile is free
+      GM_ESTAMP(13);
+      if (k + 2 < n_my) stage_e_rows(k + 2);
+      GM_ESTAMP(14);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem, 512);
+}
+
+// ---- self-test GEMM through the TMEM-operand path: out += x @ W^T (out must be zeroed by the caller) ----
+__global__ void __launch_bounds__(128, 1)
+selftest_gemm_ts_kernel(const float* __restrict__ x, const void* chunk, float* __restrict__ out, int M) {
+  extern __shared__ char smem_raw[];
+  char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const uint32_t W_s = smem_u32(base);
+  char* S = base + kChunkBytes;
+  EdgeShared* sh = reinterpret_cast<EdgeShared*>(S + kStageBytes);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t bar_w = smem_u32(&sh->w_full[0]), bar_d = smem_u32(&sh->d_ready[0]);
+  if (tid == 0) {
+    mbar_init(bar_w, 1);
+    mbar_init(bar_d, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(smem_u32(&sh->tmem_base), 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sh->tmem_base;
+  if (tid == 0) {
+    mbar_expect_tx(bar_w, kChunkBytes);
+    for (int i = 0; i < 4; ++i)
+      bulk_g2s(W_s + i * kPieceBytes, (const char*)chunk + (size_t)i * kPieceBytes, kPieceBytes, bar_w);
+  }
+  const uint32_t S_s = smem_u32(S);
+  const int r0 = warp * 32;
+  uint32_t ro[8], db[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) ro[j] = stage_chunk_off(tid, j);
+  stage_dst_init(S_s, r0, lane, db);
+  const uint32_t tD = tmem + ((uint32_t)r0 << 16), tAH = tD + 128u, tAL = tD + 192u;
+  uint32_t ph = 0;
+  const int n_tiles = M / kTile;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const size_t row0 = (size_t)tile * kTile;
+    stage_rows32_contig(db, x + (row0 + r0) * kH + 4 * lane, 32);
+    cp_async_wait_all();
+    __syncwarp();
+    row_to_operand(S, ro, tAH, tAL);
+    tmem_st_wait();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      mbar_wait(bar_w, 0);
+      tc_fence_after();
+      for (int p = 0; p < 4; ++p) issue_piece(p, W_s + p * kPieceBytes, tmem, tmem + 128u, tmem + 192u);
+      umma_commit(bar_d);
+    }
+    __syncwarp();
+    mbar_wait(bar_d, ph);
+    ph ^= 1u;
+    tc_fence_after();
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float v[32];
+      tmem_ld32(tD + c * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(S + c * kBoxBytes + ro[j]) =
+            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    __syncwarp();
+    for (int i = 0; i < 32; ++i) {
+      const float4 y = *reinterpret_cast<const float4*>(S + stage_chunk_off(r0 + i, lane));
+      red_add_v4(out + (row0 + r0 + i) * kH + 4 * lane, y);
+    }
+    tc_fence_before();
+    __syncthreads();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
+namespace {
+constexpr int kSelftestTsSmem = kChunkBytes + kStageBytes + (int)sizeof(EdgeShared) + 1024;
+}
+
+int tc_debug_stamps_edge(unsigned long long* out_host, int n) {
+#ifdef GM_STAMPS
+  GM_CUDA(cudaMemcpyFromSymbol(out_host, g_edge_stamps, sizeof(unsigned long long) * (n < 32 ? n : 32)));
+#else
+  (void)out_host; (void)n;
+#endif
+  return GM_OK;
+}
+
+int tc_configure_edge() {
+  static bool done = false;
+  if (done) return GM_OK;
+  GM_CUDA(cudaFuncSetAttribute(mp_edge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEdgeSmemBytes));
+  GM_CUDA(cudaFuncSetAttribute(selftest_gemm_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSelftestTsSmem));
+  done = true;
+  return GM_OK;
+}
+
+int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_t stream) {
+  if (g.max_edges <= 0) return GM_OK;
+  int rc = tc_configure_edge();
+  if (rc) return rc;
+  const int grid = min(ceil_div(g.max_edges, kTile), kNumSMs);
+  mp_edge_kernel<<<grid, kNTE, kEdgeSmemBytes, stream>>>(m, g, b);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("mp_edge_kernel");
+  return GM_OK;
+}
+
+int tc_selftest_gemm_ts(const float* x, const void* chunk, float* out, int M, cudaStream_t stream) {
+  GM_REQUIRE(M > 0 && M % kTile == 0, "tc_selftest_gemm_ts: M=%d must be a positive multiple of %d", M, kTile);
+  int rc = tc_configure_edge();
+  if (rc) return rc;
+  selftest_gemm_ts_kernel<<<min(M / kTile, kNumSMs), 128, kSelftestTsSmem, stream>>>(x, chunk, out, M);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("selftest_gemm_ts_kernel");
+  return GM_OK;
+}
+
+}  // namespace gm

@@ -279,17 +279,7 @@ __device__ __forceinline__ uint32_t s_off(int row, int col) {
   return (uint32_t)row * 512u + ((((uint32_t)col >> 2) ^ ((uint32_t)row & 7u)) << 4) + (((uint32_t)col & 3u) << 2);
 }
 
-// ================================================================================================
-// mp_edge: one message-passing step, edge half, one 128-edge tile per CTA iteration.
-//
-// Shared memory: A (bf16 hi/lo operand, 64 KB) | S (fp32 staging tile, 64 KB, s_off swizzle) | W (64 KB).
-// No global-load latency sits inside an epilogue: the sender projections Ps[send] are gathered into S with
-// cp.async (LDGSTS, one coalesced 512 B row per warp instruction) before the first GEMM is issued, the fp32
-// residual rows e are fetched into S the same way while layers 2 and 3 run, and the next layer's weights are
-// streamed by the TMA unit (cp.async.bulk) as soon as the GEMM that used the W buffer has committed.
-// The receiver projections Pr[recv] are read straight from L1/L2: edges are receiver-major, so the ~20
-// consecutive rows of a receiver hit the same 512 B.
-// ================================================================================================
+// ---- helpers shared by the node / encoder kernels ----
 constexpr int kPrmB1 = 0, kPrmB2 = 128, kPrmB3 = 256, kPrmG = 384, kPrmB = 512;   // offsets into Misc::w1
 
 // warp-per-row cp.async of 16 rows (512 B each) into the swizzled fp32 staging tile
@@ -340,34 +330,6 @@ __device__ __forceinline__ void epi_hidden_s(const Ctx& c, char* a, const float*
       const float4 bs = *reinterpret_cast<const float4*>(bias_s + col0 + 4 * j);
       v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f); v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
       v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f); v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w, 0.f);
-    }
-#pragma unroll
-    for (int gq = 0; gq < 4; ++gq) store_a8(a, c.row, col0 + 8 * gq, v + 8 * gq);
-  }
-}
-
-// first edge layer: A <- split(relu(D + b1 + Pr[recv] + Ps[send])); Ps rows sit in the staging tile S, this thread's
-// 64 columns of Pr[recv] start at pr_row (first 32 already in p0, loaded while the GEMM ran)
-__device__ __forceinline__ void epi_l1(const Ctx& c, char* a, const float* __restrict__ bias_s, const char* S,
-                                       const float* __restrict__ pr_row, const float4* p0) {
-  float4 p1[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) p1[j] = __ldg(reinterpret_cast<const float4*>(pr_row + 32) + j);
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const int col0 = c.hf * 64 + h * 32;
-    float v[32];
-    tmem_ld32(d_addr(c, 0, col0), v);
-    tmem_ld_wait();
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float4 bs = *reinterpret_cast<const float4*>(bias_s + col0 + 4 * j);
-      const float4 s4 = *reinterpret_cast<const float4*>(S + s_off(c.row, col0 + 4 * j));
-      const float4 p = h == 0 ? p0[j] : p1[j];
-      v[4 * j] = fmaxf(v[4 * j] + bs.x + (p.x + s4.x), 0.f);
-      v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y + (p.y + s4.y), 0.f);
-      v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z + (p.z + s4.z), 0.f);
-      v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w + (p.w + s4.w), 0.f);
     }
 #pragma unroll
     for (int gq = 0; gq < 4; ++gq) store_a8(a, c.row, col0 + 8 * gq, v + 8 * gq);
@@ -425,188 +387,6 @@ __device__ __forceinline__ void stage_params(const Ctx& c, const TcMlp& m) {
   }
 }
 
-__global__ void __launch_bounds__(NT, 1) mp_edge_kernel(TcMlp m, TcGraph g, TcBuffers b) {
-  extern __shared__ char smem_raw[];
-  Ctx c;
-  ctx_init(c, smem_raw, 2, 128);
-  char* A = c.a[0];
-  char* S = c.a[1];
-  const uint32_t S_s = c.a_s[1];
-  const float* prm = c.misc->prm;
-  stage_params(c, m);                              // published by the first launch_gemm barrier
-  const int E = min(*g.n_edges_dev, g.max_edges);
-  const int n_tiles = (E + kTile - 1) / kTile;
-  constexpr int R = kTile / (NT / 32);             // rows staged per warp
-
-  // Per-tile inputs that are fetched one tile ahead (registers): ids of this thread's row, the sender ids of the
-  // rows this warp stages, and this lane's 16 B of each of those rows of e.
-  int nx_recv = -1, nx_prev = -2, nx_send = -1;
-  float4 ereg[R];
-  auto fetch_ids = [&](int t) {
-    const int r0 = t * kTile, valid = min(kTile, E - r0);
-    nx_recv = c.row < valid ? __ldg(g.erecv + r0 + c.row) : -1;
-    nx_prev = (c.lane == 0 && c.row < valid && r0 + c.row > 0) ? __ldg(g.erecv + r0 + c.row - 1) : -2;
-    const int rl = c.warp * R + (c.lane & (R - 1));
-    nx_send = rl < valid ? __ldg(g.esend + r0 + rl) : -1;
-  };
-  auto fetch_rows = [&](int t) {
-    const int r0 = t * kTile, valid = min(kTile, E - r0);
-#pragma unroll
-    for (int i = 0; i < R; ++i) {
-      const int r = c.warp * R + i;
-      ereg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (r < valid) ereg[i] = __ldg(reinterpret_cast<const float4*>(b.e + (size_t)(r0 + r) * kH) + c.lane);
-    }
-  };
-  if ((int)blockIdx.x < n_tiles) {
-    load_w(c, m.wc[0]);
-    fetch_ids(blockIdx.x);
-    fetch_rows(blockIdx.x);
-  }
-
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int row0 = tile * kTile;
-    const int rows_valid = min(kTile, E - row0);
-    const bool has_next = tile + (int)gridDim.x < n_tiles;
-#ifdef GM_STAMPS
-    const bool stamp_on = tile == (int)blockIdx.x + (int)gridDim.x;
-#endif
-    GM_STAMP(0);
-    // ---- prologue: ids -> smem, Ps[send] rows -> S (async), e rows (registers) -> A operand ----
-    const int my_recv = nx_recv;
-    if (c.hf == 0) {
-      c.misc->recv[0][c.row] = my_recv;
-      int prev = __shfl_up_sync(0xffffffffu, my_recv, 1);
-      if (c.lane == 0) prev = nx_prev;
-      const unsigned mk = __ballot_sync(0xffffffffu, my_recv != prev);
-      if (c.lane == 0) c.misc->segmask[c.q] = mk;
-    }
-    {
-      const int sid_l = nx_send;
-      const float* ps = b.ps;
-      stage_rows_async(c, S_s, ps, [=](int, int i) -> const float* {
-        const int sid = __shfl_sync(0xffffffffu, sid_l, i);
-        return sid >= 0 ? ps + (size_t)sid * kH : nullptr;
-      });
-    }
-#pragma unroll
-    for (int i = 0; i < R; ++i) {
-      uint2 hi, lo;
-      split_bf16x2(ereg[i].x, ereg[i].y, hi.x, lo.x);
-      split_bf16x2(ereg[i].z, ereg[i].w, hi.y, lo.y);
-      const uint32_t o = a_off(c.warp * R + i, 4 * c.lane);
-      *reinterpret_cast<uint2*>(A + o) = hi;
-      *reinterpret_cast<uint2*>(A + kImageBytes + o) = lo;
-    }
-    if (has_next) fetch_ids(tile + gridDim.x);
-    GM_STAMP(1);
-    // ---- layer 1: e We^T + Pr[recv] + Ps[send] + b1 ----
-    launch_gemm(c, 0, 1, false);
-    GM_STAMP(2);
-    const float* pr_row = b.pr + (size_t)(my_recv < 0 ? 0 : my_recv) * kH + c.hf * 64;
-    float4 p0[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) p0[j] = __ldg(reinterpret_cast<const float4*>(pr_row) + j);
-    cp_async_wait_all();
-    __syncthreads();                               // every warp's share of the Ps gather is visible
-    GM_STAMP(3);
-    wait_gemm(c, 0);
-    GM_STAMP(4);
-    load_w(c, m.wc[1]);
-    epi_l1(c, A, prm + kPrmB1, S, pr_row, p0);
-    GM_STAMP(5);
-    // ---- layer 2; the fp32 residual rows travel into S meanwhile ----
-    launch_gemm(c, 0, 1, false);
-    {
-      const float* e_in = b.e;
-      stage_rows_async(c, S_s, e_in, [=](int r, int) -> const float* {
-        return r < rows_valid ? e_in + (size_t)(row0 + r) * kH : nullptr;
-      });
-    }
-    GM_STAMP(6);
-    wait_gemm(c, 0);
-    GM_STAMP(7);
-    load_w(c, m.wc[2]);
-    epi_hidden_s(c, A, prm + kPrmB2);
-    GM_STAMP(8);
-    // ---- layer 3 + LayerNorm + residual + receiver-segmented sum ----
-    cp_async_wait_all();
-    launch_gemm(c, 0, 1, false);
-    GM_STAMP(9);
-    wait_gemm(c, 0);
-    GM_STAMP(10);
-    if (has_next) load_w(c, m.wc[0]);              // next tile's first layer
-    {
-      float x[64];
-      ln_row64(c, prm, x);
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const uint32_t o = s_off(c.row, c.hf * 64 + 4 * j);
-        float4* sp = reinterpret_cast<float4*>(S + o);
-        const float4 e4 = *sp;
-        *sp = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);   // pre-residual output for the sum
-        *reinterpret_cast<float4*>(A + o) =                                       // e' = LN(...) + e (epd_gnn.py:104)
-            make_float4(x[4 * j] + e4.x, x[4 * j + 1] + e4.y, x[4 * j + 2] + e4.z, x[4 * j + 3] + e4.w);
-      }
-    }
-    GM_STAMP(11);
-    tc_fence_before();
-    __syncthreads();
-    GM_STAMP(12);
-    // e' leaves through the A region: one coalesced 512 B row per warp instruction
-    {
-      float4 o4[R];
-#pragma unroll
-      for (int i = 0; i < R; ++i) o4[i] = *reinterpret_cast<const float4*>(A + s_off(c.warp * R + i, 4 * c.lane));
-#pragma unroll
-      for (int i = 0; i < R; ++i) {
-        const int r = c.warp * R + i;
-        if (r < rows_valid) reinterpret_cast<float4*>(b.e + (size_t)(row0 + r) * kH)[c.lane] = o4[i];
-      }
-    }
-    if (has_next) fetch_rows(tile + gridDim.x);    // in flight during the column pass
-    GM_STAMP(15);
-    // column-owner pass: thread = (64-row agg tile, column).  Rows of one receiver are contiguous; the segment
-    // starts come from the bit masks, so control flow is uniform and the row loads are independent.
-    {
-      const int half = c.tid >> 7, col = c.tid & (kH - 1);
-      const int rb = half * kAggRows;
-      const int nrows = min(kAggRows, rows_valid - rb);
-      if (nrows > 0) {
-        const unsigned long long mask =
-            ((unsigned long long)c.misc->segmask[2 * half + 1] << 32) | c.misc->segmask[2 * half];
-        const int* rv = c.misc->recv[0] + rb;
-        bool cont = !(mask & 1ull);                  // row rb continues the receiver of the edge before it
-        const size_t agg_tile = (size_t)(row0 + rb) / kAggRows;
-        int r = 0;
-        while (r < nrows) {
-          const unsigned long long rest = r + 1 < 64 ? (mask >> (r + 1)) : 0ull;
-          const int end = min(rest ? r + __ffsll((long long)rest) : 64, nrows);
-          const int rid = rv[r];
-          float acc = 0.f;
-          int i = r;
-#pragma unroll 1
-          for (; i + 4 <= end; i += 4) {
-            const float y0 = *reinterpret_cast<const float*>(S + s_off(rb + i, col));
-            const float y1 = *reinterpret_cast<const float*>(S + s_off(rb + i + 1, col));
-            const float y2 = *reinterpret_cast<const float*>(S + s_off(rb + i + 2, col));
-            const float y3 = *reinterpret_cast<const float*>(S + s_off(rb + i + 3, col));
-            acc += y0; acc += y1; acc += y2; acc += y3;
-          }
-          for (; i < end; ++i) acc += *reinterpret_cast<const float*>(S + s_off(rb + i, col));
-          if (cont) b.carry[agg_tile * kH + col] = acc; else b.aggpart[(size_t)rid * kH + col] = acc;
-          cont = false;
-          r = end;
-        }
-      }
-    }
-    GM_STAMP(13);
-    __syncthreads();                                // S and recv[] are rewritten by the next tile's prologue
-    GM_STAMP(14);
-  }
-  ctx_fini(c, 128);
-}
-
 // ================================================================================================
 // Node kernels.  Shared memory: A0 (bf16 hi/lo operand) | T (second operand during layer 1, then the fp32
 // staging tile in s_off layout) | W.  Everything that leaves or enters through global memory moves as coalesced
@@ -630,13 +410,20 @@ __device__ __forceinline__ void copy_out_rows(const Ctx& c, const char* T, float
 }
 
 // this thread's half row of D -> T
-__device__ __forceinline__ void d_to_stage(const Ctx& c, char* T) {
+__device__ __forceinline__ void d_to_stage(const Ctx& c, char* T, const float* __restrict__ bias = nullptr) {
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
     const int col0 = c.hf * 64 + h * 32;
     float v[32];
     tmem_ld32(d_addr(c, 0, col0), v);
     tmem_ld_wait();
+    if (bias != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(bias + col0) + j);
+        v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
+      }
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j)
       *reinterpret_cast<float4*>(T + s_off(c.row, col0 + 4 * j)) =
@@ -674,7 +461,7 @@ __device__ __forceinline__ void node_finish(Ctx& c, char* A0, char* T, const flo
   if (!has_dec) {
     load_w(c, next.wc[4]);
     __syncthreads();                                   // every warp is done reading v' out of T
-    d_to_stage(c, T);
+    d_to_stage(c, T, next.b1);                         // Pr carries b1 of the next edge MLP (mp_edge.cu adds no bias)
     launch_gemm(c, 0, 1, false);                       // v' Ws^T
     copy_out_rows(c, T, b.pr, node0, rows_valid);
     wait_gemm(c, 0);
@@ -1012,7 +799,6 @@ int tc_configure() {
   static bool done = false;
   if (done) return GM_OK;
   int rc;
-  if ((rc = set_smem(mp_edge_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(mp_node_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(enc_node_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(enc_edge_kernel, smem_bytes(2)))) return rc;
@@ -1024,24 +810,12 @@ int tc_configure() {
 int tc_debug_stamps(unsigned long long* out_host, int n) {
 #ifdef GM_STAMPS
   GM_CUDA(cudaMemcpyFromSymbol(out_host, g_stamps, sizeof(unsigned long long) * (n < 64 ? n : 64)));
-  return GM_OK;
+  return tc_debug_stamps_edge(out_host, n);     // entries 0..31 belong to mp_edge.cu
 #else
   (void)out_host; (void)n;
   set_error("library built without -DGM_STAMPS");
   return GM_ERR_UNSUPPORTED;
 #endif
-}
-
-int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_t stream) {
-  if (g.max_edges <= 0) return GM_OK;
-  const size_t sm = smem_bytes(2);
-  int rc = tc_configure();
-  if (rc) return rc;
-  const int grid = min(ceil_div(g.max_edges, kTile), kNumSMs);
-  mp_edge_kernel<<<grid, NT, sm, stream>>>(m, g, b);
-  GM_LAUNCHED(1);
-  GM_LAUNCH_CHECK("mp_edge_kernel");
-  return GM_OK;
 }
 
 int tc_mp_node(const TcMlp& m, const TcMlp* next_edge, const TcMlp* dec, int out_dim, float* pred,

@@ -38,7 +38,7 @@ struct TcGraph {
 struct TcBuffers {
   float* e;        // [max_edges, 128] edge latents, receiver-major order, updated in place
   float* v;        // [n_nodes, 128] node latents, updated in place
-  float* pr;       // [n_nodes, 128] v @ W1[:, 128:256]^T of the *next* edge MLP (receiver term)
+  float* pr;       // [n_nodes, 128] v @ W1[:, 128:256]^T + b1 of the *next* edge MLP (receiver term)
   float* ps;       // [n_nodes, 128] v @ W1[:, 256:384]^T (sender term)
   float* aggpart;  // [n_nodes, 128] per-receiver partial sums (segment part inside its first agg tile)
   float* carry;    // [ceil(max_edges/64), 128] leading-rows partial of every 64-row agg tile
@@ -46,6 +46,7 @@ struct TcBuffers {
 
 int tc_configure();
 int tc_debug_stamps(unsigned long long* out_host, int n);   // -DGM_STAMPS builds only
+int tc_debug_stamps_edge(unsigned long long* out_host, int n);
 int tc_enc_edge(const TcMlp& m, int edge_dim, const float* pos, int pos_stride, float conn_r,
                 const float* edge_attr /*optional explicit [E,edge_dim] in receiver-major order*/,
                 const int* eref /*optional: row map into edge_attr*/, const TcGraph& g, const TcBuffers& b,
@@ -62,5 +63,7 @@ int tc_pack_chunk(const float* w, int ld, int col0, void* chunk, cudaStream_t st
 
 // Plain GEMM self-test: out[M,128] = x[M,128] @ W^T (bf16x3 split), M multiple of 128.
 int tc_selftest_gemm(const float* x, const void* chunk, float* out, int M, cudaStream_t stream);
+// Same product through the tensor-memory operand path of mp_edge.cu; accumulates into out (zero it first).
+int tc_selftest_gemm_ts(const float* x, const void* chunk, float* out, int M, cudaStream_t stream);
 
 }  // namespace gm

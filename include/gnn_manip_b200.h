@@ -207,6 +207,9 @@ int gm_debug_stamps(unsigned long long* out_host, int32_t n);
 /* tcgen05 operand-path self test: out[M,128] = x[M,128] @ w[128,128]^T (bf16x3), M % 128 == 0.
  * chunk: 64 KB device scratch for the packed weight. */
 int gm_selftest_gemm(const float* x, const float* w, void* chunk, float* out, int32_t M, void* stream);
+/* The same product through the tensor-memory operand path of the edge kernel (row bulk copies in, tcgen05.st
+ * operand, tcgen05.mma with A in TMEM, bulk reduce-add out): out += x @ w^T, so zero `out` first. */
+int gm_selftest_gemm_ts(const float* x, const float* w, void* chunk, float* out, int32_t M, void* stream);
 
 #ifdef __cplusplus
 }

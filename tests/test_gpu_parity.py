@@ -50,18 +50,24 @@ def seeded_models(gm, oracle_lib, seed=0):
 # ---------------------------------------------------------------------------------------------------------
 # tcgen05 operand path
 # ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("path", ["smem_operand", "tmem_operand"])
 @pytest.mark.parametrize("M", [128, 1024, 148 * 128 * 2 + 128])
-def test_selftest_gemm_bf16x3(gm, M):
+def test_selftest_gemm_bf16x3(gm, M, path):
     g = torch.Generator().manual_seed(M)
     x = torch.randn((M, 128), generator=g)
     w = torch.randn((128, 128), generator=g) / 11.3
     xd, wd = x.cuda(), w.cuda()
     chunk = torch.zeros(65536 + 1024, dtype=torch.uint8, device="cuda")
     off = (-chunk.data_ptr()) % 1024
-    out = torch.full((M, 128), float("nan"), device="cuda")
     L = gm._lib.lib()
-    gm._lib.check(L.gm_selftest_gemm(gm._lib.ptr(xd), gm._lib.ptr(wd), ctypes.c_void_p(chunk.data_ptr() + off),
-                                     gm._lib.ptr(out), M, gm._lib.stream_ptr()), "gm_selftest_gemm")
+    if path == "smem_operand":
+        out = torch.full((M, 128), float("nan"), device="cuda")
+        fn, name = L.gm_selftest_gemm, "gm_selftest_gemm"
+    else:                                  # accumulates through the bulk reduce-add: starts from zero
+        out = torch.zeros((M, 128), device="cuda")
+        fn, name = L.gm_selftest_gemm_ts, "gm_selftest_gemm_ts"
+    gm._lib.check(fn(gm._lib.ptr(xd), gm._lib.ptr(wd), ctypes.c_void_p(chunk.data_ptr() + off),
+                     gm._lib.ptr(out), M, gm._lib.stream_ptr()), name)
     torch.cuda.synchronize()
     ref = x.double() @ w.double().T
     err = rel_l2(out.cpu(), ref)

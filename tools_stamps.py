@@ -13,6 +13,7 @@ st = (ctypes.c_ulonglong * 64)()
 gm._lib.check(gm._lib.lib().gm_debug_stamps(st, 64), "gm_debug_stamps")
 s = np.array(st[:], dtype=np.int64)
 print("kernel ms", per, "E", E)
-print("stamps (cycles since stamp 0):", [int(x - s[0]) for x in s[:24]])
-print("deltas:", [int(s[i + 1] - s[i]) for i in range(23)])
+print("edge compute stamps (cycles since stamp 0):", [int(x - s[0]) for x in s[:16]])
+print("edge compute deltas:", [int(s[i + 1] - s[i]) for i in range(15)])
+print("edge mma stamps (before/after a_ready wait per (layer,slot); since first):", [int(x - s[16]) for x in s[16:28]])
 print("node stamps:", [int(x - s[32]) for x in s[32:44]])
