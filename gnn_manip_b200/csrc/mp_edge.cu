@@ -30,24 +30,26 @@ namespace gm {
 
 namespace {
 
-constexpr int kNTE = 320;
-constexpr int kPieceBytes = 16384;           // one K block (64 columns) of one 128-row bf16 image
-constexpr int kRing = 5;                     // weight pieces resident
+constexpr int kNTE = 256;                    // two compute warpgroups; one elected thread per slot issues the MMAs
+constexpr int kPieceBytes = 16384;           // one K block (64 columns) of one 128-row bf16 image (self test)
+constexpr int kWBlock = 8192;                // this CTA's 64 weight rows of one K block of one image
+constexpr int kWLayer = 4 * kWBlock;         // {Wh.k0, Wh.k1, Wl.k0, Wl.k1}
+constexpr int kWBytes = 3 * kWLayer;         // all three layers stay resident: 96 KB per CTA of the pair
 constexpr int kBoxBytes = kTile * 128;       // one 32-column box of the staging tile
 constexpr int kStageBytes = 4 * kBoxBytes;   // 64 KB
-constexpr uint32_t kIdescE = umma_idesc_bf16(kTile, kH);
+constexpr uint32_t kIdescE = umma_idesc_bf16(kTile, kH);          // M = 128 (self test, one CTA)
+constexpr uint32_t kIdescPair = umma_idesc_bf16(2 * kTile, kH);   // M = 256 across the CTA pair
 
 struct EdgeShared {
-  uint64_t w_full[kRing];
-  uint64_t w_free[kRing];
-  uint64_t a_ready[2];                       // operand of the next GEMM is in TMEM (4 warp arrivals)
-  uint64_t d_ready[2];                       // accumulator complete (tcgen05.commit)
+  uint64_t w_full;                           // this CTA's 96 KB of weights landed
+  uint64_t a_ready[2];                       // leader CTA: operand of the next GEMM is in TMEM (4 + 4 warp arrivals)
+  uint64_t d_ready[2];                       // accumulator complete (multicast tcgen05.commit)
   uint32_t tmem_base;
   uint32_t pad;
   uint32_t segmask[2][4];                    // bit l of word q: row 32q+l starts a new receiver segment
   alignas(16) float prm[4 * kH];             // b2 | b3 | LayerNorm gamma | LayerNorm beta
 };
-constexpr int kEdgeSmemBytes = kRing * kPieceBytes + 2 * kStageBytes + (int)sizeof(EdgeShared) + 1024;
+constexpr int kEdgeSmemBytes = kWBytes + 2 * kStageBytes + (int)sizeof(EdgeShared);
 static_assert(kEdgeSmemBytes <= 232448, "mp_edge shared memory exceeds 227 KB");
 
 // Staging tile addressing.  Element (row, col): box col >> 5, then row * 128 + ((chunk ^ (row & 7)) << 4) + (col & 3) * 4
@@ -96,6 +98,86 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// ---- CTA-pair (cluster of 2) helpers ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity), "r"(20000u)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait_cluster(bar, parity)) return;
+  uint32_t spins = 0;
+  while (!mbar_try_wait_cluster(bar, parity)) {
+    if (++spins > (1u << 18)) {
+      printf("gnn_manip_b200: cluster mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t ncols) {  // one warp of EACH CTA
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D (+)= A x B^T over the CTA pair: M = 256 (128 rows of A from each CTA's TMEM), B rows split 64 + 64 between the
+// two CTAs' shared memories at the same offset, D rows land in each CTA's own TMEM
+__device__ __forceinline__ void umma_bf16_ts_pair(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                                  uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      :
+      : "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {   // arrives on `bar` in both CTAs
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"((uint16_t)3)
+      : "memory");
+}
+// one whole layer GEMM of a slot (24 MMAs): w_layer_s = this CTA's {Wh.k0, Wh.k1, Wl.k0, Wl.k1} blocks of the layer
+__device__ __forceinline__ void issue_layer_pair(uint32_t w_layer_s, uint32_t tD, uint32_t tAH, uint32_t tAL) {
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    const uint32_t wb = w_layer_s + p * kWBlock, kcol = (uint32_t)(p & 1) * 32u;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks)
+      umma_bf16_ts_pair(tD, tAH + kcol + ks * 8, umma_desc_sw128(wb + ks * 32), kIdescPair, (p | ks) ? 1u : 0u);
+    if (p < 2) {
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks)
+        umma_bf16_ts_pair(tD, tAL + kcol + ks * 8, umma_desc_sw128(wb + ks * 32), kIdescPair, 1u);
+    }
+  }
+}
+
 // 32 lanes x 16 columns: thread i of the warp writes TMEM lane (base_lane + i), columns [col, col + 16)
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
   asm volatile(
@@ -155,11 +237,12 @@ __device__ __forceinline__ void row_to_operand(const char* S, const uint32_t* ro
   }
 }
 
-__device__ __forceinline__ void publish_operand(uint32_t bar_a, int lane) {
+// this warp's rows of the next A operand are in TMEM: tell the leader CTA's issuer (cluster-space barrier address)
+__device__ __forceinline__ void publish_operand(uint32_t bar_a_leader, int lane) {
   tmem_st_wait();
   tc_fence_before();
   __syncwarp();
-  if (lane == 0) mbar_arrive(bar_a);
+  if (lane == 0) mbar_arrive_cluster(bar_a_leader);
 }
 
 // Phase timestamps (debug aid, -DGM_STAMPS): thread 0 of CTA 0 (slot 0) records clock64() during its third tile,
@@ -176,28 +259,32 @@ constexpr int kOffB2 = 0, kOffB3 = 128, kOffG = 256, kOffBeta = 384;
 }  // namespace
 
 __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, TcBuffers b) {
-  extern __shared__ char smem_raw[];
-  char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  extern __shared__ __align__(1024) char smem_raw[];
+  char* base = smem_raw;
   const uint32_t W_s = smem_u32(base);
-  char* S_base = base + kRing * kPieceBytes;
+  char* S_base = base + kWBytes;
   EdgeShared* sh = reinterpret_cast<EdgeShared*>(S_base + 2 * kStageBytes);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-
+  const uint32_t rank = cluster_ctarank();     // 0: leader (issues the pair's MMAs), 1: peer
+  if (tid == 0 && (W_s & 1023u) != 0u) {
+    printf("gnn_manip_b200: mp_edge dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
   if (tid == 0) {
-    for (int i = 0; i < kRing; ++i) {
-      mbar_init(smem_u32(&sh->w_full[i]), 1);
-      mbar_init(smem_u32(&sh->w_free[i]), 1);
-    }
+    mbar_init(smem_u32(&sh->w_full), 1);
     for (int s = 0; s < 2; ++s) {
-      mbar_init(smem_u32(&sh->a_ready[s]), 4);
+      mbar_init(smem_u32(&sh->a_ready[s]), 8);
       mbar_init(smem_u32(&sh->d_ready[s]), 1);
     }
     fence_mbar_init();
+    // this CTA's half (rows 64 rank .. 64 rank + 63) of every K block of every image of the three layers
+    mbar_expect_tx(smem_u32(&sh->w_full), kWBytes);
+    for (int l = 0; l < 3; ++l)
+      for (int p = 0; p < 4; ++p)
+        bulk_g2s(W_s + l * kWLayer + p * kWBlock, (const char*)m.wc[l] + (size_t)p * kPieceBytes + rank * kWBlock,
+                 kWBlock, smem_u32(&sh->w_full));
   }
-  if (warp == 8) {
-    tmem_alloc(smem_u32(&sh->tmem_base), 512);
-    tmem_relinquish();
-  }
+  if (warp == 0) tmem_alloc_pair(smem_u32(&sh->tmem_base), 512);
   for (int i = tid; i < kH; i += kNTE) {
     sh->prm[kOffB2 + i] = m.b2[i];
     sh->prm[kOffB3 + i] = m.b3[i];
@@ -212,57 +299,11 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
   const int E = min(*g.n_edges_dev, g.max_edges);
   const int n_tiles = (E + kTile - 1) / kTile;
   const int grid = (int)gridDim.x;
-  const int n_my = (int)blockIdx.x < n_tiles ? (n_tiles - (int)blockIdx.x + grid - 1) / grid : 0;
-  const int n_pairs = (n_my + 1) >> 1;
-
-  if (warp == 9) {
-    // ---------------- weight producer ----------------
-    if (lane == 0) {
-      int n = 0;
-      for (int j = 0; j < n_pairs; ++j)
-        for (int l = 0; l < 3; ++l)
-          for (int p = 0; p < 4; ++p, ++n) {
-            const int slot = n % kRing;
-            if (n >= kRing) mbar_wait(smem_u32(&sh->w_free[slot]), (uint32_t)((n / kRing) - 1) & 1u);
-            const uint32_t bar = smem_u32(&sh->w_full[slot]);
-            mbar_expect_tx(bar, kPieceBytes);
-            bulk_g2s(W_s + slot * kPieceBytes, (const char*)m.wc[l] + (size_t)p * kPieceBytes, kPieceBytes, bar);
-          }
-    }
-    __syncwarp();
-  } else if (warp == 8) {
-    // ---------------- MMA issuer ----------------
-    if (lane == 0) {
-      uint32_t pa[2] = {0u, 0u};
-      int n = 0;
-      for (int j = 0; j < n_pairs; ++j) {
-        const int nt = min(2, n_my - 2 * j);
-        for (int l = 0; l < 3; ++l) {
-          for (int s = 0; s < nt; ++s) {
-#ifdef GM_STAMPS
-            const bool stamp_on = blockIdx.x == 0 && j == 2;
-#endif
-            GM_ESTAMP(16 + (l * 2 + s) * 2);
-            mbar_wait(smem_u32(&sh->a_ready[s]), pa[s]);
-            pa[s] ^= 1u;
-            tc_fence_after();
-            GM_ESTAMP(17 + (l * 2 + s) * 2);
-            const uint32_t tD = tmem + 256u * s, tAH = tD + 128u, tAL = tD + 192u;
-#pragma unroll
-            for (int p = 0; p < 4; ++p) {
-              const int idx = n + p, slot = idx % kRing;
-              mbar_wait(smem_u32(&sh->w_full[slot]), (uint32_t)(idx / kRing) & 1u);
-              issue_piece(p, W_s + slot * kPieceBytes, tD, tAH, tAL);
-              if (s == nt - 1) umma_commit(smem_u32(&sh->w_free[slot]));
-            }
-            umma_commit(smem_u32(&sh->d_ready[s]));
-          }
-          n += 4;
-        }
-      }
-    }
-    __syncwarp();
-  } else {
+  // both CTAs of a pair run the same number of tile iterations (the leader's count); a CTA without a tile for an
+  // iteration still takes part in every hand-off with zero valid rows
+  const int b_lead = (int)blockIdx.x - (int)rank;
+  const int n_my = b_lead < n_tiles ? (n_tiles - b_lead + grid - 1) / grid : 0;
+  {
     // ---------------- compute warpgroups: slot s, thread = edge row r ----------------
     const int s = warp >> 2, q = warp & 3, r = tid & (kTile - 1), r0 = q * 32;
     char* S = S_base + s * kStageBytes;
@@ -271,9 +312,25 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
 #pragma unroll
     for (int j = 0; j < 8; ++j) ro[j] = stage_chunk_off(r, j);
     const uint32_t tD = tmem + ((uint32_t)r0 << 16) + 256u * s, tAH = tD + 128u, tAL = tD + 192u;
-    const uint32_t bar_a = smem_u32(&sh->a_ready[s]), bar_d = smem_u32(&sh->d_ready[s]);
+    const uint32_t bar_a_local = smem_u32(&sh->a_ready[s]), bar_d = smem_u32(&sh->d_ready[s]);
+    const uint32_t bar_a = mapa_shared(bar_a_local, 0);   // the leader CTA's barrier, cluster address space
+    const bool issuer = rank == 0 && q == 0 && lane == 0;
     const float* prm = sh->prm;
-    uint32_t ph_d = 0;
+    uint32_t ph_d = 0, ph_a = 0;
+    int layer = 0;
+    // leader, one thread per slot: once both CTAs have published the operand, issue the layer's 24 MMAs for the
+    // pair and commit to d_ready in both CTAs.  The two slots' issuers interleave on the tensor pipe in readiness order.
+    auto issue_gemm = [&]() {
+      if (issuer) {
+        mbar_wait_cluster(bar_a_local, ph_a);
+        tc_fence_after();
+        issue_layer_pair(W_s + layer * kWLayer, tmem + 256u * s, tmem + 256u * s + 128u, tmem + 256u * s + 192u);
+        umma_commit_pair(bar_d);
+      }
+      ph_a ^= 1u;
+      layer = layer == 2 ? 0 : layer + 1;
+      __syncwarp();
+    };
 
     int nx_recv = -1, nx_send = -1, nx_prev = -2;
     auto fetch_ids = [&](int k) {
@@ -290,12 +347,15 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     stage_dst_init(S_s, r0, lane, db);
     auto stage_e_rows = [&](int k) {           // this warp's 32 rows of tile k
       const int ge0 = (blockIdx.x + k * grid) * kTile + r0;
-      stage_rows32_contig(db, b.e + (size_t)ge0 * kH + 4 * lane, E - ge0);
+      stage_rows32_contig(db, b.e + (size_t)(ge0 < E ? ge0 : 0) * kH + 4 * lane, E - ge0);
     };
     if (s < n_my) {
       fetch_ids(s);
       stage_e_rows(s);
     }
+    // weights of this CTA landed; peer barriers initialised, peer weights landed, TMEM of the pair allocated
+    mbar_wait(smem_u32(&sh->w_full), 0);
+    cluster_sync_all();
     for (int k = s; k < n_my; k += 2) {
       const int row0 = (blockIdx.x + k * grid) * kTile;
       const int rows_valid = min(kTile, E - row0);
@@ -330,12 +390,13 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       GM_ESTAMP(2);
       stage_rows32_gather(db, b.ps + 4 * lane, my_send);
       publish_operand(bar_a, lane);
+      issue_gemm();
       GM_ESTAMP(3);
       // ---- layer 1 epilogue: relu(D + Pr[recv] (b1 folded in) + Ps[send]) ----
       cp_async_wait_all();
       __syncwarp();
       GM_ESTAMP(4);
-      mbar_wait(bar_d, ph_d);
+      mbar_wait_cluster(bar_d, ph_d);
       ph_d ^= 1u;
       tc_fence_after();
       GM_ESTAMP(5);
@@ -358,9 +419,10 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
         put_operand32(v, tAH, tAL, c);
       }
       publish_operand(bar_a, lane);
+      issue_gemm();
       GM_ESTAMP(6);
       // ---- layer 2 epilogue: relu(D + b2) ----
-      mbar_wait(bar_d, ph_d);
+      mbar_wait_cluster(bar_d, ph_d);
       ph_d ^= 1u;
       tc_fence_after();
       GM_ESTAMP(7);
@@ -380,9 +442,10 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
         put_operand32(v, tAH, tAL, c);
       }
       publish_operand(bar_a, lane);
+      issue_gemm();
       GM_ESTAMP(8);
       // ---- layer 3 epilogue: y = LayerNorm(D + b3) -> staging row (two sweeps over the accumulator in TMEM) ----
-      mbar_wait(bar_d, ph_d);
+      mbar_wait_cluster(bar_d, ph_d);
       ph_d ^= 1u;
       tc_fence_after();
       GM_ESTAMP(9);
@@ -514,8 +577,8 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     }
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 8) tmem_dealloc(tmem, 512);
+  cluster_sync_all();                          // the peer may still be arriving on / reading through this CTA
+  if (warp == 0) tmem_dealloc_pair(tmem, 512);
 }
 
 // ---- self-test GEMM through the TMEM-operand path: out += x @ W^T (out must be zeroed by the caller) ----
@@ -527,7 +590,7 @@ selftest_gemm_ts_kernel(const float* __restrict__ x, const void* chunk, float* _
   char* S = base + kChunkBytes;
   EdgeShared* sh = reinterpret_cast<EdgeShared*>(S + kStageBytes);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint32_t bar_w = smem_u32(&sh->w_full[0]), bar_d = smem_u32(&sh->d_ready[0]);
+  const uint32_t bar_w = smem_u32(&sh->w_full), bar_d = smem_u32(&sh->d_ready[0]);
   if (tid == 0) {
     mbar_init(bar_w, 1);
     mbar_init(bar_d, 1);
@@ -623,8 +686,21 @@ int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_
   if (g.max_edges <= 0) return GM_OK;
   int rc = tc_configure_edge();
   if (rc) return rc;
-  const int grid = min(ceil_div(g.max_edges, kTile), kNumSMs);
-  mp_edge_kernel<<<grid, kNTE, kEdgeSmemBytes, stream>>>(m, g, b);
+  // CTA pairs (clusters of 2): even grid, at most one CTA per SM
+  const int grid = min((ceil_div(g.max_edges, kTile) + 1) & ~1, kNumSMs & ~1);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kNTE);
+  cfg.dynamicSmemBytes = kEdgeSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  GM_CUDA(cudaLaunchKernelEx(&cfg, mp_edge_kernel, m, g, b));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("mp_edge_kernel");
   return GM_OK;
