@@ -89,6 +89,10 @@ __device__ __forceinline__ void stage_rows32_gather(const uint32_t* db, const fl
 }
 
 __device__ __forceinline__ void red_add_v4(float* gdst, const float4& v) {
+#ifdef GM_EXP_STG   // timing experiment only (wrong results): plain store instead of the reduction
+  *reinterpret_cast<float4*>(gdst) = v;
+  return;
+#endif
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(gdst), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
                : "memory");
 }
@@ -248,6 +252,9 @@ __device__ __forceinline__ void publish_operand(uint32_t bar_a_leader, int lane)
 // Phase timestamps (debug aid, -DGM_STAMPS): thread 0 of CTA 0 (slot 0) records clock64() during its third tile,
 // the MMA issuer during the matching pair; read back with gm_debug_stamps() (entries 0..31).
 #ifdef GM_STAMPS
+#ifndef GM_STAMP_TID
+#define GM_STAMP_TID 0
+#endif
 __device__ unsigned long long g_edge_stamps[32];
 #define GM_ESTAMP(i) do { if (stamp_on) g_edge_stamps[i] = clock64(); } while (0)
 #else
@@ -349,6 +356,32 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       const int ge0 = (blockIdx.x + k * grid) * kTile + r0;
       stage_rows32_contig(db, b.e + (size_t)(ge0 < E ? ge0 : 0) * kH + 4 * lane, E - ge0);
     };
+    int cur_recv = -1, cur_send = -1, cur_prev = -2;
+    const float* pr_row = b.pr;
+    // e rows of a tile (already landed in this warp's staging rows) -> bf16 hi / lo operand of layer 1 in TMEM
+    auto operand_from_stage = [&]() {
+      cp_async_wait_all();
+      __syncwarp();
+      row_to_operand(S, ro, tAH, tAL);
+      tmem_st_wait();
+      __syncwarp();                            // every lane is done reading this warp's rows
+    };
+    // Starts tile k: its layer-1 operand is in TMEM and the staging rows are free.  Segment mask, Pr prefetch,
+    // the Ps[send] gather into the staging rows (lands while GEMM 1 runs), operand hand-off, GEMM 1.
+    auto begin_tile = [&](int k) {
+      cur_recv = nx_recv; cur_send = nx_send; cur_prev = nx_prev;
+      const int ge = (blockIdx.x + k * grid) * kTile + r;
+      {
+        const unsigned mk = __ballot_sync(0xffffffffu, cur_recv != cur_prev);
+        if (lane == 0) sh->segmask[s][q] = mk;
+      }
+      pr_row = b.pr + (size_t)(ge < E ? cur_recv : 0) * kH;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) prefetch_l1(pr_row + 32 * i);
+      stage_rows32_gather(db, b.ps + 4 * lane, cur_send);
+      publish_operand(bar_a, lane);
+      issue_gemm();
+    };
     if (s < n_my) {
       fetch_ids(s);
       stage_e_rows(s);
@@ -356,42 +389,19 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     // weights of this CTA landed; peer barriers initialised, peer weights landed, TMEM of the pair allocated
     mbar_wait(smem_u32(&sh->w_full), 0);
     cluster_sync_all();
+    if (s < n_my) {
+      operand_from_stage();
+      begin_tile(s);
+    }
     for (int k = s; k < n_my; k += 2) {
       const int row0 = (blockIdx.x + k * grid) * kTile;
       const int rows_valid = min(kTile, E - row0);
-      const bool live = r < rows_valid;
-      const int my_recv = nx_recv, my_send = nx_send, my_prev = nx_prev;
+      const bool has_next = k + 2 < n_my;
 #ifdef GM_STAMPS
-      const bool stamp_on = blockIdx.x == 0 && tid == 0 && k == 4;
+      const bool stamp_on = blockIdx.x == 0 && tid == GM_STAMP_TID && k == 4;
 #endif
       GM_ESTAMP(0);
-      if (k + 2 < n_my) {
-        fetch_ids(k + 2);
-        // pull the e rows of the tile after next towards L2: lane -> (row r0 + 8 i + lane / 4, 128 B line lane % 4)
-        const int ge0 = (blockIdx.x + (k + 2) * grid) * kTile + r0 + (lane >> 2);
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          if (ge0 + 8 * i < E) prefetch_l2(b.e + (size_t)(ge0 + 8 * i) * kH + (lane & 3) * 32);
-      }
-      {
-        const unsigned mk = __ballot_sync(0xffffffffu, my_recv != my_prev);
-        if (lane == 0) sh->segmask[s][q] = mk;
-      }
-      const float* pr_row = b.pr + (size_t)(live ? my_recv : 0) * kH;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) prefetch_l1(pr_row + 32 * i);
-      // ---- operand of layer 1: e rows -> bf16 hi / lo in TMEM; then the Ps[send] gather reuses the staging rows ----
-      cp_async_wait_all();
-      __syncwarp();
-      GM_ESTAMP(1);
-      row_to_operand(S, ro, tAH, tAL);
-      tmem_st_wait();
-      __syncwarp();                            // every lane is done reading this warp's rows
-      GM_ESTAMP(2);
-      stage_rows32_gather(db, b.ps + 4 * lane, my_send);
-      publish_operand(bar_a, lane);
-      issue_gemm();
-      GM_ESTAMP(3);
+      if (has_next) fetch_ids(k + 2);
       // ---- layer 1 epilogue: relu(D + Pr[recv] (b1 folded in) + Ps[send]) ----
       cp_async_wait_all();
       __syncwarp();
@@ -400,89 +410,119 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       ph_d ^= 1u;
       tc_fence_after();
       GM_ESTAMP(5);
+      {
+        // accumulator blocks are fetched one ahead (tcgen05.ld is asynchronous; the wait sits after the math of
+        // the previous block), Pr comes from L1 (prefetched at the top of the tile)
+        float va[32], vb[32];
+        float4 pa[8], pb[8];
+        auto load_pr = [&](int c, float4* p) {
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float v[32];
-        tmem_ld32(tD + c * 32, v);
-        float4 p[8];
+          for (int j = 0; j < 8; ++j) p[j] = __ldg(reinterpret_cast<const float4*>(pr_row + c * 32) + j);
+        };
+        auto e1_block = [&](int c, float* v, const float4* p) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) p[j] = __ldg(reinterpret_cast<const float4*>(pr_row + c * 32) + j);
+          for (int j = 0; j < 8; ++j) {
+            const float4 s4 = *reinterpret_cast<const float4*>(S + c * kBoxBytes + ro[j]);
+            v[4 * j] = fmaxf(v[4 * j] + (p[j].x + s4.x), 0.f);
+            v[4 * j + 1] = fmaxf(v[4 * j + 1] + (p[j].y + s4.y), 0.f);
+            v[4 * j + 2] = fmaxf(v[4 * j + 2] + (p[j].z + s4.z), 0.f);
+            v[4 * j + 3] = fmaxf(v[4 * j + 3] + (p[j].w + s4.w), 0.f);
+          }
+          put_operand32(v, tAH, tAL, c);
+        };
+        tmem_ld32(tD, va);
+        load_pr(0, pa);
+        load_pr(1, pb);
         tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 s4 = *reinterpret_cast<const float4*>(S + c * kBoxBytes + ro[j]);
-          v[4 * j] = fmaxf(v[4 * j] + (p[j].x + s4.x), 0.f);
-          v[4 * j + 1] = fmaxf(v[4 * j + 1] + (p[j].y + s4.y), 0.f);
-          v[4 * j + 2] = fmaxf(v[4 * j + 2] + (p[j].z + s4.z), 0.f);
-          v[4 * j + 3] = fmaxf(v[4 * j + 3] + (p[j].w + s4.w), 0.f);
-        }
-        put_operand32(v, tAH, tAL, c);
+        tmem_ld32(tD + 32, vb);
+        e1_block(0, va, pa);
+        load_pr(2, pa);
+        tmem_ld_wait();
+        tmem_ld32(tD + 64, va);
+        e1_block(1, vb, pb);
+        load_pr(3, pb);
+        tmem_ld_wait();
+        tmem_ld32(tD + 96, vb);
+        e1_block(2, va, pa);
+        tmem_ld_wait();
+        e1_block(3, vb, pb);
       }
       publish_operand(bar_a, lane);
       issue_gemm();
+      // the staging rows are free until the LayerNorm rows go in: the e rows of this slot's next tile land here
+      // while layers 2 and 3 run
+      if (has_next) stage_e_rows(k + 2);
       GM_ESTAMP(6);
       // ---- layer 2 epilogue: relu(D + b2) ----
       mbar_wait_cluster(bar_d, ph_d);
       ph_d ^= 1u;
       tc_fence_after();
       GM_ESTAMP(7);
+      {
+        float va[32], vb[32];
+        auto e2_block = [&](int c, float* v) {
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float v[32];
-        tmem_ld32(tD + c * 32, v);
+          for (int j = 0; j < 8; ++j) {
+            const float4 bs = *reinterpret_cast<const float4*>(prm + kOffB2 + c * 32 + 4 * j);
+            v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f);
+            v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
+            v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f);
+            v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w, 0.f);
+          }
+          put_operand32(v, tAH, tAL, c);
+        };
+        tmem_ld32(tD, va);
         tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 bs = *reinterpret_cast<const float4*>(prm + kOffB2 + c * 32 + 4 * j);
-          v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f);
-          v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
-          v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f);
-          v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w, 0.f);
-        }
-        put_operand32(v, tAH, tAL, c);
+        tmem_ld32(tD + 32, vb);
+        e2_block(0, va);
+        tmem_ld_wait();
+        tmem_ld32(tD + 64, va);
+        e2_block(1, vb);
+        tmem_ld_wait();
+        tmem_ld32(tD + 96, vb);
+        e2_block(2, va);
+        tmem_ld_wait();
+        e2_block(3, vb);
       }
       publish_operand(bar_a, lane);
       issue_gemm();
       GM_ESTAMP(8);
-      // ---- layer 3 epilogue: y = LayerNorm(D + b3) -> staging row (two sweeps over the accumulator in TMEM) ----
+      // ---- layer 3 epilogue: y = LayerNorm(D + b3) -> staging row ----
       mbar_wait_cluster(bar_d, ph_d);
       ph_d ^= 1u;
       tc_fence_after();
       GM_ESTAMP(9);
+      if (has_next) operand_from_stage();      // the A region is free (GEMM 3 is complete); D is read right below
+      GM_ESTAMP(2);
       {
-        float sa = 0.f, sb = 0.f, qa = 0.f, qb = 0.f;
+        // the whole accumulator row lives in registers: exact two-pass LayerNorm, thread-local
+        float x[kH];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          float v[32];
-          tmem_ld32(tD + c * 32, v);
-          tmem_ld_wait();
+        for (int c = 0; c < 4; ++c) tmem_ld32(tD + c * 32, x + c * 32);
+        tmem_ld_wait();
+        float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 t = *reinterpret_cast<const float4*>(prm + kOffB3 + c * 32 + 4 * j);
-            const float x0 = v[4 * j] + t.x, x1 = v[4 * j + 1] + t.y, x2 = v[4 * j + 2] + t.z, x3 = v[4 * j + 3] + t.w;
-            sa += x0; sb += x1; sa += x2; sb += x3;
-            qa = fmaf(x0, x0, qa); qb = fmaf(x1, x1, qb); qa = fmaf(x2, x2, qa); qb = fmaf(x3, x3, qb);
-          }
+        for (int j = 0; j < kH / 4; ++j) {
+          const float4 t = *reinterpret_cast<const float4*>(prm + kOffB3 + 4 * j);
+          x[4 * j] += t.x; x[4 * j + 1] += t.y; x[4 * j + 2] += t.z; x[4 * j + 3] += t.w;
+          sa += x[4 * j]; sb += x[4 * j + 1]; sc += x[4 * j + 2]; sd += x[4 * j + 3];
         }
-        const float mean = (sa + sb) * (1.0f / kH);
-        const float var = fmaxf((qa + qb) * (1.0f / kH) - mean * mean, 0.f);
-        const float rstd = 1.0f / sqrtf(var + 1e-5f);
+        const float mean = ((sa + sb) + (sc + sd)) * (1.0f / kH);
+        float qa = 0.f, qb = 0.f, qc = 0.f, qd = 0.f;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          float v[32];
-          tmem_ld32(tD + c * 32, v);
-          tmem_ld_wait();
+        for (int j = 0; j < kH / 4; ++j) {
+          x[4 * j] -= mean; x[4 * j + 1] -= mean; x[4 * j + 2] -= mean; x[4 * j + 3] -= mean;
+          qa = fmaf(x[4 * j], x[4 * j], qa); qb = fmaf(x[4 * j + 1], x[4 * j + 1], qb);
+          qc = fmaf(x[4 * j + 2], x[4 * j + 2], qc); qd = fmaf(x[4 * j + 3], x[4 * j + 3], qd);
+        }
+        const float rstd = 1.0f / sqrtf(((qa + qb) + (qc + qd)) * (1.0f / kH) + 1e-5f);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 t = *reinterpret_cast<const float4*>(prm + kOffB3 + c * 32 + 4 * j);
-            const float4 g4 = *reinterpret_cast<const float4*>(prm + kOffG + c * 32 + 4 * j);
-            const float4 b4 = *reinterpret_cast<const float4*>(prm + kOffBeta + c * 32 + 4 * j);
-            *reinterpret_cast<float4*>(S + c * kBoxBytes + ro[j]) =
-                make_float4(((v[4 * j] + t.x) - mean) * rstd * g4.x + b4.x,
-                            ((v[4 * j + 1] + t.y) - mean) * rstd * g4.y + b4.y,
-                            ((v[4 * j + 2] + t.z) - mean) * rstd * g4.z + b4.z,
-                            ((v[4 * j + 3] + t.w) - mean) * rstd * g4.w + b4.w);
-          }
+        for (int j = 0; j < kH / 4; ++j) {
+          const float4 g4 = *reinterpret_cast<const float4*>(prm + kOffG + 4 * j);
+          const float4 b4 = *reinterpret_cast<const float4*>(prm + kOffBeta + 4 * j);
+          *reinterpret_cast<float4*>(S + (j >> 3) * kBoxBytes + ro[j & 7]) =
+              make_float4(x[4 * j] * rstd * g4.x + b4.x, x[4 * j + 1] * rstd * g4.y + b4.y,
+                          x[4 * j + 2] * rstd * g4.z + b4.z, x[4 * j + 3] * rstd * g4.w + b4.w);
         }
       }
       __syncwarp();
@@ -503,76 +543,84 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       }
       named_bar_sync(1 + s, kTile);
       GM_ESTAMP(11);
-      // ---- receiver-segmented sum of the pre-residual rows: thread = column r, two 64-row halves interleaved,
-      //      8 + 8 rows loaded per step; segment starts come from the bit masks, so control flow is uniform ----
+      // ---- receiver-segmented sum of the pre-residual rows (scatter_sum, gn_utils.py:60-64): thread = column r.
+      //      Sweep A: running sum along the rows of each 64-row half, restarted at segment starts and written back
+      //      in place at segment ends (uniform bit masks, no data-dependent branches, strictly sequential fp32 order).
+      //      Sweep B: one store per segment end -> aggpart[receiver] (or carry[] for a segment that began before
+      //      this 64-row block). ----
       {
         const uint32_t cbase = (uint32_t)(r >> 5) * kBoxBytes + ((uint32_t)r & 3u) * 4u;
         const uint32_t cchunk = ((uint32_t)r >> 2) & 7u;
         uint32_t co[8];
 #pragma unroll
         for (int ii = 0; ii < 8; ++ii) co[ii] = cbase + ((cchunk ^ (uint32_t)ii) << 4);
-        const int n0 = min(kAggRows, rows_valid), n1 = max(0, min(kAggRows, rows_valid - kAggRows));
-        const unsigned long long m0 = (((unsigned long long)sh->segmask[s][1] << 32) | sh->segmask[s][0]) & ~1ull;
-        const unsigned long long m1 = (((unsigned long long)sh->segmask[s][3] << 32) | sh->segmask[s][2]) & ~1ull;
-        const size_t t0 = (size_t)row0 / kAggRows;
-        const int* erecv_t = g.erecv + row0;
+        const int n0 = max(0, min(kAggRows, rows_valid)), n1 = max(0, min(kAggRows, rows_valid - kAggRows));
+        const unsigned long long f0 = ((unsigned long long)sh->segmask[s][1] << 32) | sh->segmask[s][0];
+        const unsigned long long f1 = ((unsigned long long)sh->segmask[s][3] << 32) | sh->segmask[s][2];
+        const unsigned long long v0 = n0 >= 64 ? ~0ull : ((1ull << n0) - 1ull), v1 = n1 >= 64 ? ~0ull : ((1ull << n1) - 1ull);
+        const unsigned long long m0 = f0 & ~1ull & v0, m1 = f1 & ~1ull & v1;              // restart points
+        const unsigned long long e0 = ((m0 >> 1) | (n0 > 0 ? 1ull << (n0 - 1) : 0ull)) & v0;   // segment ends
+        const unsigned long long e1 = ((m1 >> 1) | (n1 > 0 ? 1ull << (n1 - 1) : 0ull)) & v1;
         float a0 = 0.f, a1 = 0.f;
-        bool c0 = !(sh->segmask[s][0] & 1u), c1 = !(sh->segmask[s][2] & 1u);   // row continues the previous agg tile
-        // receiver id of the running segment, fetched when the segment starts (used one segment later)
-        int id0 = n0 > 0 ? __ldg(erecv_t) : 0, id1 = n1 > 0 ? __ldg(erecv_t + kAggRows) : 0;
-        auto flush = [&](float acc, bool cont, int rid, size_t agg_tile) {
-          if (cont) b.carry[agg_tile * kH + r] = acc;
-          else b.aggpart[(size_t)rid * kH + r] = acc;
-        };
 #pragma unroll 1
         for (int bb = 0; bb < kAggRows / 8; ++bb) {
           float y0[8], y1[8];
-          const char* p = S + bb * 1024;
+          char* p = S + bb * 1024;
 #pragma unroll
           for (int ii = 0; ii < 8; ++ii) {
             y0[ii] = *reinterpret_cast<const float*>(p + co[ii] + ii * 128);
             y1[ii] = *reinterpret_cast<const float*>(p + kAggRows * 128 + co[ii] + ii * 128);
           }
-          const unsigned mb0 = (unsigned)(m0 >> (8 * bb)) & 0xffu, mb1 = (unsigned)(m1 >> (8 * bb)) & 0xffu;
-          const int nb0 = n0 - 8 * bb, nb1 = n1 - 8 * bb;
-          if (mb0 == 0u && nb0 >= 8) {
+          const unsigned sb0 = (unsigned)(m0 >> (8 * bb)) & 0xffu, eb0 = (unsigned)(e0 >> (8 * bb)) & 0xffu;
+          const unsigned sb1 = (unsigned)(m1 >> (8 * bb)) & 0xffu, eb1 = (unsigned)(e1 >> (8 * bb)) & 0xffu;
+          if ((sb0 | eb0) == 0u) {
 #pragma unroll
             for (int ii = 0; ii < 8; ++ii) a0 += y0[ii];
           } else {
 #pragma unroll
             for (int ii = 0; ii < 8; ++ii) {
-              if (ii < nb0) {
-                if ((mb0 >> ii) & 1u) {
-                  flush(a0, c0, id0, t0);
-                  a0 = 0.f; c0 = false; id0 = __ldg(erecv_t + 8 * bb + ii);
-                }
-                a0 += y0[ii];
-              }
+              const float t = a0 + y0[ii];
+              a0 = ((sb0 >> ii) & 1u) ? y0[ii] : t;
+              if ((eb0 >> ii) & 1u) *reinterpret_cast<float*>(p + co[ii] + ii * 128) = a0;
             }
           }
-          if (mb1 == 0u && nb1 >= 8) {
+          if ((sb1 | eb1) == 0u) {
 #pragma unroll
             for (int ii = 0; ii < 8; ++ii) a1 += y1[ii];
           } else {
 #pragma unroll
             for (int ii = 0; ii < 8; ++ii) {
-              if (ii < nb1) {
-                if ((mb1 >> ii) & 1u) {
-                  flush(a1, c1, id1, t0 + 1);
-                  a1 = 0.f; c1 = false; id1 = __ldg(erecv_t + kAggRows + 8 * bb + ii);
-                }
-                a1 += y1[ii];
-              }
+              const float t = a1 + y1[ii];
+              a1 = ((sb1 >> ii) & 1u) ? y1[ii] : t;
+              if ((eb1 >> ii) & 1u) *reinterpret_cast<float*>(p + kAggRows * 128 + co[ii] + ii * 128) = a1;
             }
           }
         }
-        if (n0 > 0) flush(a0, c0, id0, t0);
-        if (n1 > 0) flush(a1, c1, id1, t0 + 1);
+        // Sweep B: the warp that owns an end row stores its 512 B of segment sums (coalesced); the receiver id comes
+        // from the owning lane's register
+        named_bar_sync(1 + s, kTile);
+        {
+          const unsigned long long eh = q < 2 ? e0 : e1, fh = q < 2 ? f0 : f1;
+          unsigned ends = (unsigned)(eh >> ((q & 1) * 32));
+          // the first end of a 64-row block belongs to a segment that began in the previous block iff its flag bit 0 is clear
+          const bool cont_first = !(fh & 1ull) && ((q & 1) == 0 || (unsigned)eh == 0u);
+          const size_t agg_tile = (size_t)row0 / kAggRows + (q >> 1);
+          bool first = true;
+          while (ends != 0u) {
+            const int i = __ffs((int)ends) - 1;
+            ends &= ends - 1u;
+            const int rid = __shfl_sync(0xffffffffu, cur_recv, i);
+            const float4 v = *reinterpret_cast<const float4*>(S + (db[i & 7] - S_s) + (i & ~7) * 128);
+            float* dst = (first && cont_first) ? b.carry + agg_tile * kH : b.aggpart + (size_t)rid * kH;
+            *reinterpret_cast<float4*>(dst + 4 * lane) = v;
+            first = false;
+          }
+        }
       }
       GM_ESTAMP(12);
       named_bar_sync(1 + s, kTile);            // every row has been read: the slot's staging tile is free
       GM_ESTAMP(13);
-      if (k + 2 < n_my) stage_e_rows(k + 2);
+      if (has_next) begin_tile(k + 2);
       GM_ESTAMP(14);
     }
   }

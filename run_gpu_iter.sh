@@ -15,3 +15,8 @@ PY
 tail -n 5 gpurun_out/bench_quick.err
 make -s -C gnn_manip_b200/csrc clean all EXTRA=-DGM_STAMPS > gpurun_out/stamps_build.log 2>&1
 timeout 300 python tools_stamps.py 100000 > gpurun_out/stamps_c3.txt 2>&1; tail -6 gpurun_out/stamps_c3.txt
+if [ -n "$GM_EXP" ]; then
+  make -s -C gnn_manip_b200/csrc clean all EXTRA="-DGM_STAMPS $GM_EXP" > gpurun_out/stamps_build2.log 2>&1
+  echo "== experiment build: $GM_EXP"
+  timeout 300 python tools_stamps.py 100000 > gpurun_out/stamps_c3_exp.txt 2>&1; tail -6 gpurun_out/stamps_c3_exp.txt | head -3
+fi
