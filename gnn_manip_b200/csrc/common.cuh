@@ -72,6 +72,33 @@ struct Arena {
 };
 
 #ifdef __CUDACC__
+// Launch with programmatic stream serialization (and an optional cluster width): the kernel may start while its
+// predecessor in the stream drains; it calls pdl_wait() before touching upstream data.
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t stream,
+                                     int cluster_x, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[n].val.programmaticStreamSerializationAllowed = 1;
+  ++n;
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster_x;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ---------------------------------------------------------------------------------------------
 // PTX wrappers: mbarrier, bulk async copy (TMA unit), proxy fences, tcgen05 / TMEM
 // ---------------------------------------------------------------------------------------------
@@ -204,6 +231,12 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
                : "memory");
 }
+
+// ---- programmatic dependent launch: the kernels of one model step are chained so that the next kernel's
+// prologue (barrier init, TMEM allocation, parameter / weight staging -- constant data only) overlaps the tail of
+// the previous kernel.  pdl_wait() must precede the first access to anything an earlier kernel of the stream wrote.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // ---- bf16 hi/lo split of an fp32 pair: x ~= hi + lo with |err| <~ 2^-17 |x| ----
 __device__ __forceinline__ void split_bf16x2(float a, float b, uint32_t& hi, uint32_t& lo) {

@@ -302,6 +302,8 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = sh->tmem_base;
+  pdl_launch_dependents();
+  pdl_wait();                                  // everything above touched constant parameters only
 
   const int E = min(*g.n_edges_dev, g.max_edges);
   const int n_tiles = (E + kTile - 1) / kTile;
@@ -736,19 +738,7 @@ int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_
   if (rc) return rc;
   // CTA pairs (clusters of 2): even grid, at most one CTA per SM
   const int grid = min((ceil_div(g.max_edges, kTile) + 1) & ~1, kNumSMs & ~1);
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kNTE);
-  cfg.dynamicSmemBytes = kEdgeSmemBytes;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  GM_CUDA(cudaLaunchKernelEx(&cfg, mp_edge_kernel, m, g, b));
+  GM_CUDA(launch_pdl(mp_edge_kernel, grid, kNTE, (size_t)kEdgeSmemBytes, stream, 2, m, g, b));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("mp_edge_kernel");
   return GM_OK;

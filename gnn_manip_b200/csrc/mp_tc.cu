@@ -532,6 +532,8 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
   constexpr int R = kTile / (NT / 32);
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
   if ((int)blockIdx.x < n_tiles) load_w(c, m.wc[0]);
+  pdl_launch_dependents();
+  pdl_wait();                                      // everything above reads constant parameters only
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
@@ -632,6 +634,8 @@ enc_node_kernel(TcMlp m, TcMlp next, int node_dim, const float* __restrict__ nod
   __syncthreads();
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
   if ((int)blockIdx.x < n_tiles) load_w(c, m.wc[2]);
+  pdl_launch_dependents();
+  pdl_wait();
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
@@ -683,6 +687,8 @@ enc_edge_kernel(TcMlp m, int edge_dim, const float* __restrict__ pos, int pos_st
   stage_params(c, m);
   for (int i = c.tid; i < kH * edge_dim; i += NT) c.misc->w1[i] = m.w1[i];
   __syncthreads();
+  pdl_launch_dependents();
+  pdl_wait();
   const int E = min(*g.n_edges_dev, g.max_edges);
   const int n_tiles = (E + kTile - 1) / kTile;
   // this thread's input row of a tile: explicit edge_attr row, or the displacement features built from positions
@@ -826,7 +832,7 @@ int tc_mp_node(const TcMlp& m, const TcMlp* next_edge, const TcMlp* dec, int out
   int rc = tc_configure();
   if (rc) return rc;
   const int grid = min(ceil_div(g.n_nodes, kTile), kNumSMs);
-  mp_node_kernel<<<grid, NT, sm, stream>>>(m, dec ? *dec : *next_edge, dec ? 1 : 0, out_dim, pred, g, b);
+  GM_CUDA(launch_pdl(mp_node_kernel, grid, NT, sm, stream, 1, m, dec ? *dec : *next_edge, dec ? 1 : 0, out_dim, pred, g, b));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("mp_node_kernel");
   return GM_OK;
@@ -839,7 +845,7 @@ int tc_enc_node(const TcMlp& m, const TcMlp& next_edge, int node_dim, const floa
   int rc = tc_configure();
   if (rc) return rc;
   const int grid = min(ceil_div(g.n_nodes, kTile), kNumSMs);
-  enc_node_kernel<<<grid, NT, sm, stream>>>(m, next_edge, node_dim, nodes, g, b);
+  GM_CUDA(launch_pdl(enc_node_kernel, grid, NT, sm, stream, 1, m, next_edge, node_dim, nodes, g, b));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("enc_node_kernel");
   return GM_OK;
@@ -855,7 +861,7 @@ int tc_enc_edge(const TcMlp& m, int edge_dim, const float* pos, int pos_stride, 
   int rc = tc_configure();
   if (rc) return rc;
   const int grid = min(ceil_div(g.max_edges, kTile), kNumSMs);
-  enc_edge_kernel<<<grid, NT, sm, stream>>>(m, edge_dim, pos, pos_stride, conn_r, edge_attr, eref, g, b);
+  GM_CUDA(launch_pdl(enc_edge_kernel, grid, NT, sm, stream, 1, m, edge_dim, pos, pos_stride, conn_r, edge_attr, eref, g, b));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("enc_edge_kernel");
   return GM_OK;
