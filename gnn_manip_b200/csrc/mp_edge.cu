@@ -436,21 +436,28 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
         load_pr(0, pa);
         load_pr(1, pb);
         tmem_ld_wait();
+        GM_ESTAMP(16);
         tmem_ld32(tD + 32, vb);
         e1_block(0, va, pa);
+        GM_ESTAMP(17);
         load_pr(2, pa);
         tmem_ld_wait();
         tmem_ld32(tD + 64, va);
         e1_block(1, vb, pb);
+        GM_ESTAMP(18);
         load_pr(3, pb);
         tmem_ld_wait();
         tmem_ld32(tD + 96, vb);
         e1_block(2, va, pa);
+        GM_ESTAMP(19);
         tmem_ld_wait();
         e1_block(3, vb, pb);
+        GM_ESTAMP(20);
       }
       publish_operand(bar_a, lane);
+      GM_ESTAMP(21);
       issue_gemm();
+      GM_ESTAMP(22);
       // the staging rows are free until the LayerNorm rows go in: the e rows of this slot's next tile land here
       // while layers 2 and 3 run
       if (has_next) stage_e_rows(k + 2);
@@ -631,6 +638,194 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
   if (warp == 0) tmem_dealloc_pair(tmem, 512);
 }
 
+// ================================================================================================
+// enc_edge (pair version): edge encoder of EncProcDecGNN.forward (epd_gnn.py:30-33,88) on the same CTA-pair
+// pipeline.  Edge features (row A2, utils.py:43-61) are built on the fly from positions; Linear(4,128)+ReLU runs
+// on CUDA cores straight into the TMEM operand, the two 128x128 layers on the tensor cores with both weight chunks
+// resident, LayerNorm in registers, e rows leave through this warp's staging rows as coalesced 512 B stores.
+// No cross-warp hand-off exists inside a CTA besides the MMA barriers.
+// ================================================================================================
+__global__ void __launch_bounds__(kNTE, 1)
+enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, float conn_r, TcGraph g, TcBuffers b) {
+  extern __shared__ __align__(1024) char smem_raw[];
+  char* base = smem_raw;
+  const uint32_t W_s = smem_u32(base);
+  float4* w1s = reinterpret_cast<float4*>(base + 2 * kWLayer);          // [128] rows of the 4-wide first layer
+  float* b1s = reinterpret_cast<float*>(base + 2 * kWLayer + kH * 16);  // [128]
+  char* S_base = base + kWBytes;
+  EdgeShared* sh = reinterpret_cast<EdgeShared*>(S_base + 2 * kStageBytes);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = cluster_ctarank();
+  if (tid == 0) {
+    mbar_init(smem_u32(&sh->w_full), 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(smem_u32(&sh->a_ready[s]), 8);
+      mbar_init(smem_u32(&sh->d_ready[s]), 1);
+    }
+    fence_mbar_init();
+    mbar_expect_tx(smem_u32(&sh->w_full), 2 * kWLayer);
+    for (int l = 0; l < 2; ++l)
+      for (int p = 0; p < 4; ++p)
+        bulk_g2s(W_s + l * kWLayer + p * kWBlock, (const char*)m.wc[2 + l] + (size_t)p * kPieceBytes + rank * kWBlock,
+                 kWBlock, smem_u32(&sh->w_full));
+  }
+  if (warp == 0) tmem_alloc_pair(smem_u32(&sh->tmem_base), 512);
+  for (int i = tid; i < kH; i += kNTE) {
+    sh->prm[kOffB2 + i] = m.b2[i];
+    sh->prm[kOffB3 + i] = m.b3[i];
+    sh->prm[kOffG + i] = m.ln_g[i];
+    sh->prm[kOffBeta + i] = m.ln_b[i];
+    w1s[i] = make_float4(m.w1[4 * i], m.w1[4 * i + 1], m.w1[4 * i + 2], m.w1[4 * i + 3]);
+    b1s[i] = m.b1[i];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sh->tmem_base;
+  pdl_launch_dependents();
+  pdl_wait();
+
+  const int E = min(*g.n_edges_dev, g.max_edges);
+  const int n_tiles = (E + kTile - 1) / kTile;
+  const int grid = (int)gridDim.x;
+  const int b_lead = (int)blockIdx.x - (int)rank;
+  const int n_my = b_lead < n_tiles ? (n_tiles - b_lead + grid - 1) / grid : 0;
+  const int s = warp >> 2, q = warp & 3, r = tid & (kTile - 1), r0 = q * 32;
+  char* S = S_base + s * kStageBytes;
+  const uint32_t S_s = smem_u32(S);
+  uint32_t ro[8], db[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) ro[j] = stage_chunk_off(r, j);
+  stage_dst_init(S_s, r0, lane, db);
+  const uint32_t tD = tmem + ((uint32_t)r0 << 16) + 256u * s, tAH = tD + 128u, tAL = tD + 192u;
+  const uint32_t bar_a_local = smem_u32(&sh->a_ready[s]), bar_d = smem_u32(&sh->d_ready[s]);
+  const uint32_t bar_a = mapa_shared(bar_a_local, 0);
+  const bool issuer = rank == 0 && q == 0 && lane == 0;
+  const float* prm = sh->prm;
+  uint32_t ph_d = 0, ph_a = 0;
+  int layer = 0;
+  auto issue_gemm = [&]() {
+    if (issuer) {
+      mbar_wait_cluster(bar_a_local, ph_a);
+      tc_fence_after();
+      issue_layer_pair(W_s + layer * kWLayer, tmem + 256u * s, tmem + 256u * s + 128u, tmem + 256u * s + 192u);
+      umma_commit_pair(bar_d);
+    }
+    ph_a ^= 1u;
+    layer ^= 1;
+    __syncwarp();
+  };
+  auto load_x = [&](int k) -> float4 {
+    const int ge = (blockIdx.x + k * grid) * kTile + r;
+    if (ge < E) return edge_feature(pos, pos_stride, __ldg(g.esend + ge), __ldg(g.erecv + ge), conn_r);
+    return make_float4(0.f, 0.f, 0.f, 0.f);
+  };
+  float4 xn = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (s < n_my) xn = load_x(s);
+  mbar_wait(smem_u32(&sh->w_full), 0);
+  cluster_sync_all();
+  for (int k = s; k < n_my; k += 2) {
+    const int row0 = (blockIdx.x + k * grid) * kTile;
+    const int rows_valid = min(kTile, E - row0);
+    const float4 x = xn;
+    if (k + 2 < n_my) xn = load_x(k + 2);          // in flight during this tile
+    // ---- layer 1 on CUDA cores: relu(W1 x + b1) -> bf16 hi / lo operand in TMEM (same FMA order as the SIMT path) ----
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float4 w = w1s[c * 32 + j];
+        v[j] = fmaxf(fmaf(x.w, w.w, fmaf(x.z, w.z, fmaf(x.y, w.y, fmaf(x.x, w.x, b1s[c * 32 + j])))), 0.f);
+      }
+      put_operand32(v, tAH, tAL, c);
+    }
+    publish_operand(bar_a, lane);
+    issue_gemm();
+    // ---- layer 2 epilogue: relu(D + b2) ----
+    mbar_wait_cluster(bar_d, ph_d);
+    ph_d ^= 1u;
+    tc_fence_after();
+    {
+      float va[32], vb[32];
+      auto e2_block = [&](int c, float* v) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 bs = *reinterpret_cast<const float4*>(prm + kOffB2 + c * 32 + 4 * j);
+          v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f);
+          v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
+          v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f);
+          v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w, 0.f);
+        }
+        put_operand32(v, tAH, tAL, c);
+      };
+      tmem_ld32(tD, va);
+      tmem_ld_wait();
+      tmem_ld32(tD + 32, vb);
+      e2_block(0, va);
+      tmem_ld_wait();
+      tmem_ld32(tD + 64, va);
+      e2_block(1, vb);
+      tmem_ld_wait();
+      tmem_ld32(tD + 96, vb);
+      e2_block(2, va);
+      tmem_ld_wait();
+      e2_block(3, vb);
+    }
+    publish_operand(bar_a, lane);
+    issue_gemm();
+    // ---- layer 3 epilogue: e0 = LayerNorm(D + b3) -> this thread's staging row ----
+    mbar_wait_cluster(bar_d, ph_d);
+    ph_d ^= 1u;
+    tc_fence_after();
+    {
+      float y[kH];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld32(tD + c * 32, y + c * 32);
+      tmem_ld_wait();
+      float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
+#pragma unroll
+      for (int j = 0; j < kH / 4; ++j) {
+        const float4 t = *reinterpret_cast<const float4*>(prm + kOffB3 + 4 * j);
+        y[4 * j] += t.x; y[4 * j + 1] += t.y; y[4 * j + 2] += t.z; y[4 * j + 3] += t.w;
+        sa += y[4 * j]; sb += y[4 * j + 1]; sc += y[4 * j + 2]; sd += y[4 * j + 3];
+      }
+      const float mean = ((sa + sb) + (sc + sd)) * (1.0f / kH);
+      float qa = 0.f, qb = 0.f, qc = 0.f, qd = 0.f;
+#pragma unroll
+      for (int j = 0; j < kH / 4; ++j) {
+        y[4 * j] -= mean; y[4 * j + 1] -= mean; y[4 * j + 2] -= mean; y[4 * j + 3] -= mean;
+        qa = fmaf(y[4 * j], y[4 * j], qa); qb = fmaf(y[4 * j + 1], y[4 * j + 1], qb);
+        qc = fmaf(y[4 * j + 2], y[4 * j + 2], qc); qd = fmaf(y[4 * j + 3], y[4 * j + 3], qd);
+      }
+      const float rstd = 1.0f / sqrtf(((qa + qb) + (qc + qd)) * (1.0f / kH) + 1e-5f);
+#pragma unroll
+      for (int j = 0; j < kH / 4; ++j) {
+        const float4 g4 = *reinterpret_cast<const float4*>(prm + kOffG + 4 * j);
+        const float4 b4 = *reinterpret_cast<const float4*>(prm + kOffBeta + 4 * j);
+        *reinterpret_cast<float4*>(S + (j >> 3) * kBoxBytes + ro[j & 7]) =
+            make_float4(y[4 * j] * rstd * g4.x + b4.x, y[4 * j + 1] * rstd * g4.y + b4.y,
+                        y[4 * j + 2] * rstd * g4.z + b4.z, y[4 * j + 3] * rstd * g4.w + b4.w);
+      }
+    }
+    __syncwarp();
+    // ---- this warp's 32 rows leave as coalesced 512 B stores ----
+    {
+      const int nr = min(32, rows_valid - r0);
+      float* e_out = b.e + (size_t)(row0 + r0) * kH + 4 * lane;
+#pragma unroll 8
+      for (int i = 0; i < 32; ++i)
+        if (i < nr)
+          *reinterpret_cast<float4*>(e_out + i * kH) =
+              *reinterpret_cast<const float4*>(S + (db[i & 7] - S_s) + (i & ~7) * 128);
+    }
+    __syncwarp();                                  // the rows are rewritten by this warp's next tile
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 0) tmem_dealloc_pair(tmem, 512);
+}
+
 // ---- self-test GEMM through the TMEM-operand path: out += x @ W^T (out must be zeroed by the caller) ----
 __global__ void __launch_bounds__(128, 1)
 selftest_gemm_ts_kernel(const float* __restrict__ x, const void* chunk, float* __restrict__ out, int M) {
@@ -727,6 +922,7 @@ int tc_configure_edge() {
   static bool done = false;
   if (done) return GM_OK;
   GM_CUDA(cudaFuncSetAttribute(mp_edge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEdgeSmemBytes));
+  GM_CUDA(cudaFuncSetAttribute(enc_edge_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEdgeSmemBytes));
   GM_CUDA(cudaFuncSetAttribute(selftest_gemm_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSelftestTsSmem));
   done = true;
   return GM_OK;
@@ -741,6 +937,20 @@ int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_
   GM_CUDA(launch_pdl(mp_edge_kernel, grid, kNTE, (size_t)kEdgeSmemBytes, stream, 2, m, g, b));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("mp_edge_kernel");
+  return GM_OK;
+}
+
+// on-the-fly edge features (edge_dim == 4): the CTA-pair pipeline
+int tc_enc_edge_pair(const TcMlp& m, const float* pos, int pos_stride, float conn_r, const TcGraph& g,
+                     const TcBuffers& b, cudaStream_t stream) {
+  if (g.max_edges <= 0) return GM_OK;
+  int rc = tc_configure_edge();
+  if (rc) return rc;
+  const int grid = min((ceil_div(g.max_edges, kTile) + 1) & ~1, kNumSMs & ~1);
+  GM_CUDA(launch_pdl(enc_edge_pair_kernel, grid, kNTE, (size_t)kEdgeSmemBytes, stream, 2, m, pos, pos_stride, conn_r,
+                     g, b));
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("enc_edge_pair_kernel");
   return GM_OK;
 }
 

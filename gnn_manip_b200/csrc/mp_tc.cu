@@ -857,6 +857,7 @@ int tc_enc_edge(const TcMlp& m, int edge_dim, const float* pos, int pos_stride, 
   GM_REQUIRE(edge_dim >= 1 && edge_dim <= kMaxIn1, "tc_enc_edge: edge_dim=%d outside [1,%d]", edge_dim, kMaxIn1);
   GM_REQUIRE(edge_attr != nullptr || edge_dim == 4, "tc_enc_edge: on-the-fly edge features need edge_dim == 4");
   if (g.max_edges <= 0) return GM_OK;
+  if (edge_attr == nullptr) return tc_enc_edge_pair(m, pos, pos_stride, conn_r, g, b, stream);
   const size_t sm = smem_bytes(2);
   int rc = tc_configure();
   if (rc) return rc;
