@@ -115,29 +115,26 @@ __device__ __forceinline__ void fence_mbar_init() {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-// One try_wait with a suspend-time hint: the hardware parks the thread until the phase completes or ~the hint (ns)
-// has passed, so a waiting warp does not compete for issue slots with the warps doing the work.
+// mbarrier.try_wait parks the thread in hardware until the phase completes or a short system time limit expires
+// (no suspend-time hint: with a hint ptxas emits NANOSLEEP back-off loops whose wake-up latency is microseconds).
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(bar), "r"(parity), "r"(20000u)
+      : "r"(bar), "r"(parity)
       : "memory");
   return ok != 0;
 }
 // Bounded wait: a protocol bug must trap (kills the context with an error) instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 18)) {
-      printf("gnn_manip_b200: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-      __trap();
-    }
-  }
+#pragma unroll 1
+  for (uint32_t spins = 0; spins < (1u << 26); ++spins)
+    if (mbar_try_wait(bar, parity)) return;
+  printf("gnn_manip_b200: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+  __trap();
 }
 
 // generic-proxy writes to shared memory -> visible to the async proxy (UMMA / bulk copy)

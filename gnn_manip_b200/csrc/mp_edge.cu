@@ -117,28 +117,7 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
   return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity), "r"(20000u)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait_cluster(bar, parity)) return;
-  uint32_t spins = 0;
-  while (!mbar_try_wait_cluster(bar, parity)) {
-    if (++spins > (1u << 18)) {
-      printf("gnn_manip_b200: cluster mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-      __trap();
-    }
-  }
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t ncols) {  // one warp of EACH CTA
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols)
@@ -331,7 +310,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     // pair and commit to d_ready in both CTAs.  The two slots' issuers interleave on the tensor pipe in readiness order.
     auto issue_gemm = [&]() {
       if (issuer) {
-        mbar_wait_cluster(bar_a_local, ph_a);
+        mbar_wait(bar_a_local, ph_a);
         tc_fence_after();
         issue_layer_pair(W_s + layer * kWLayer, tmem + 256u * s, tmem + 256u * s + 128u, tmem + 256u * s + 192u);
         umma_commit_pair(bar_d);
@@ -408,7 +387,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       cp_async_wait_all();
       __syncwarp();
       GM_ESTAMP(4);
-      mbar_wait_cluster(bar_d, ph_d);
+      mbar_wait(bar_d, ph_d);
       ph_d ^= 1u;
       tc_fence_after();
       GM_ESTAMP(5);
@@ -463,7 +442,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       if (has_next) stage_e_rows(k + 2);
       GM_ESTAMP(6);
       // ---- layer 2 epilogue: relu(D + b2) ----
-      mbar_wait_cluster(bar_d, ph_d);
+      mbar_wait(bar_d, ph_d);
       ph_d ^= 1u;
       tc_fence_after();
       GM_ESTAMP(7);
@@ -497,7 +476,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       issue_gemm();
       GM_ESTAMP(8);
       // ---- layer 3 epilogue: y = LayerNorm(D + b3) -> staging row ----
-      mbar_wait_cluster(bar_d, ph_d);
+      mbar_wait(bar_d, ph_d);
       ph_d ^= 1u;
       tc_fence_after();
       GM_ESTAMP(9);
@@ -706,7 +685,7 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
   int layer = 0;
   auto issue_gemm = [&]() {
     if (issuer) {
-      mbar_wait_cluster(bar_a_local, ph_a);
+      mbar_wait(bar_a_local, ph_a);
       tc_fence_after();
       issue_layer_pair(W_s + layer * kWLayer, tmem + 256u * s, tmem + 256u * s + 128u, tmem + 256u * s + 192u);
       umma_commit_pair(bar_d);
@@ -743,7 +722,7 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
     publish_operand(bar_a, lane);
     issue_gemm();
     // ---- layer 2 epilogue: relu(D + b2) ----
-    mbar_wait_cluster(bar_d, ph_d);
+    mbar_wait(bar_d, ph_d);
     ph_d ^= 1u;
     tc_fence_after();
     {
@@ -775,7 +754,7 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
     publish_operand(bar_a, lane);
     issue_gemm();
     // ---- layer 3 epilogue: e0 = LayerNorm(D + b3) -> this thread's staging row ----
-    mbar_wait_cluster(bar_d, ph_d);
+    mbar_wait(bar_d, ph_d);
     ph_d ^= 1u;
     tc_fence_after();
     {
