@@ -1,28 +1,33 @@
-// Row A3 (+ the scatter_add of A4) -- edge half of one message-passing step, warp-specialised and software-pipelined.
+// Row A3 (+ the scatter_add of A4) -- edge half of one message-passing step (and the edge encoder) on CTA pairs.
 //
 // Replaces EdgeModel.forward (deps/torch-graphnet/torch_graphnet/graph_networks.py:29-50), the residual of
 // EncProcDecGNN._process (gnn_manip/models/epd_gnn.py:104) and scatter_sum (utils/gn_utils.py:60-64).
 //
-// One persistent CTA per SM, 320 threads:
+// Persistent CTA pairs (clusters of 2, one CTA per SM), 256 threads per CTA:
 //   warps 0-3  compute warpgroup of tile slot 0   } thread = one edge row of a 128-edge tile: operand split,
 //   warps 4-7  compute warpgroup of tile slot 1   } bias/ReLU/LayerNorm epilogues, segmented receiver sum
-//   warp  8    tcgen05.mma issuer (one thread)
-//   warp  9    weight producer (one thread, cp.async.bulk through the TMA unit)
-// Two 128-edge tiles are in flight per SM; while one tile's accumulator is in an epilogue the tensor core works on
-// the other tile (G_l(slot 0), G_l(slot 1), G_l+1(slot 0), ...), so both tiles share every weight piece.
+// Each CTA has two 128-edge tiles in flight (one per warpgroup).  A layer of a slot runs as ONE M = 256 GEMM over
+// the pair (tcgen05.mma.cta_group::2): 128 rows of A from each CTA's tensor memory, the weight rows split 64 + 64
+// between the two CTAs' shared memories.  Halving the weights per CTA is what lets all three layers (bf16 hi + lo,
+// 96 KB per CTA) stay resident for the whole kernel: no weight streaming, no weight traffic in L2 after the prologue.
+// The leader CTA's lane 0 of each slot's first warp issues the slot's MMAs once both CTAs have published the
+// operand (remote mbarrier arrive), and commits to the d_ready barrier of both CTAs (multicast); the two slots'
+// GEMMs interleave on the tensor pipe in readiness order while the other slot's warps run their epilogue.
 //
 // Memory plan
 //   TMEM (512 columns): per slot 128 fp32 accumulator columns + the A operand of the next GEMM as bf16 hi / lo
 //     images (64 + 64 columns, lane = edge row, two K elements per 32-bit column).  Epilogues write the next A
 //     operand straight into TMEM with tcgen05.st -- no swizzled shared-memory operand, no st.shared bandwidth --
 //     and the MMAs read A from TMEM and only the weights from shared memory.
-//   SMEM: ring of 16 KB weight pieces {Wh.k0, Wh.k1, Wl.k0, Wl.k1} per layer, refilled piece by piece as soon as
-//     the second tile has consumed one; one 64 KB fp32 staging tile per slot, stored as four 32-column boxes of
-//     128 x 128 B with the 16-byte chunk index XOR (row & 7): conflict-free for row-owner 128-bit access and for
-//     column-owner 32-bit access.  Each warp stages exactly the 32 rows its own threads own (cp.async, one
-//     coalesced 512 B row per instruction: e rows in, then the Ps[send] gather), so those hand-offs are
-//     warp-local; LayerNorm rows leave as vector reductions into e (red.global.add.v4.f32: e' = e + LN(...), the
-//     residual is added in L2 and the fp32 residual never enters the SM a second time).
+//   SMEM: 96 KB of weights; one 64 KB fp32 staging tile per slot, stored as four 32-column boxes of 128 x 128 B
+//     with the 16-byte chunk index XOR (row & 7): conflict-free for row-owner 128-bit access and for column-owner
+//     32-bit access.  Each warp stages exactly the 32 rows its own threads own (cp.async, one coalesced 512 B row
+//     per instruction), so those hand-offs are warp-local: the Ps[send] gather lands while GEMM 1 runs, the e rows
+//     of the slot's NEXT tile land while layers 2-3 run and are converted to the next operand before LayerNorm
+//     overwrites the rows.  LayerNorm rows leave as vector reductions into e (red.global.add.v4.f32: e' = e +
+//     LN(...), the residual is added in L2 and the fp32 residual never enters the SM a second time).
+//   Segmented receiver sum: column-owner sweep over the staged rows (running sums restarted by uniform bit masks,
+//     written back in place at segment ends), then one coalesced 512 B store per segment by the warp owning the row.
 //   bf16x3: x.w ~= xh.wh + xl.wh + xh.wl, accumulated in fp32 in TMEM.
 #include "mp_tc.cuh"
 
@@ -241,6 +246,11 @@ __device__ unsigned long long g_edge_stamps[32];
 #endif
 
 constexpr int kOffB2 = 0, kOffB3 = 128, kOffG = 256, kOffBeta = 384;
+#ifdef GM_EXP_NOPRM
+#define GM_PRM4(ptr) make_float4(0.5f, 0.25f, 0.125f, 1.5f)
+#else
+#define GM_PRM4(ptr) (*reinterpret_cast<const float4*>(ptr))
+#endif
 
 }  // namespace
 
@@ -281,8 +291,15 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = sh->tmem_base;
+#ifdef GM_STAMPS
+  if (blockIdx.x == 0 && tid == 0) g_edge_stamps[23] = clock64();
+#endif
   pdl_launch_dependents();
-  pdl_wait();                                  // everything above touched constant parameters only
+  pdl_wait();
+#ifdef GM_STAMPS
+  if (blockIdx.x == 0 && tid == 0) g_edge_stamps[24] = clock64();
+#endif
+                                 // everything above touched constant parameters only
 
   const int E = min(*g.n_edges_dev, g.max_edges);
   const int n_tiles = (E + kTile - 1) / kTile;
@@ -294,6 +311,11 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
   {
     // ---------------- compute warpgroups: slot s, thread = edge row r ----------------
     const int s = warp >> 2, q = warp & 3, r = tid & (kTile - 1), r0 = q * 32;
+#ifdef GM_EXP_ONESLOT   // timing experiment: slot 1 idle, slot 0 takes every tile
+    const int KSTEP = 1, K0 = s == 0 ? 0 : (1 << 30);
+#else
+    const int KSTEP = 2, K0 = s;
+#endif
     char* S = S_base + s * kStageBytes;
     const uint32_t S_s = smem_u32(S);
     uint32_t ro[8];                            // row-owner offsets of the 8 chunks of a box
@@ -363,26 +385,26 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       publish_operand(bar_a, lane);
       issue_gemm();
     };
-    if (s < n_my) {
-      fetch_ids(s);
-      stage_e_rows(s);
+    if (K0 < n_my) {
+      fetch_ids(K0);
+      stage_e_rows(K0);
     }
     // weights of this CTA landed; peer barriers initialised, peer weights landed, TMEM of the pair allocated
     mbar_wait(smem_u32(&sh->w_full), 0);
     cluster_sync_all();
-    if (s < n_my) {
+    if (K0 < n_my) {
       operand_from_stage();
-      begin_tile(s);
+      begin_tile(K0);
     }
-    for (int k = s; k < n_my; k += 2) {
+    for (int k = K0; k < n_my; k += KSTEP) {
       const int row0 = (blockIdx.x + k * grid) * kTile;
       const int rows_valid = min(kTile, E - row0);
-      const bool has_next = k + 2 < n_my;
+      const bool has_next = k + KSTEP < n_my;
 #ifdef GM_STAMPS
       const bool stamp_on = blockIdx.x == 0 && tid == GM_STAMP_TID && k == 4;
 #endif
       GM_ESTAMP(0);
-      if (has_next) fetch_ids(k + 2);
+      if (has_next) fetch_ids(k + KSTEP);
       // ---- layer 1 epilogue: relu(D + Pr[recv] (b1 folded in) + Ps[send]) ----
       cp_async_wait_all();
       __syncwarp();
@@ -439,7 +461,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       GM_ESTAMP(22);
       // the staging rows are free until the LayerNorm rows go in: the e rows of this slot's next tile land here
       // while layers 2 and 3 run
-      if (has_next) stage_e_rows(k + 2);
+      if (has_next) stage_e_rows(k + KSTEP);
       GM_ESTAMP(6);
       // ---- layer 2 epilogue: relu(D + b2) ----
       mbar_wait(bar_d, ph_d);
@@ -451,7 +473,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
         auto e2_block = [&](int c, float* v) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float4 bs = *reinterpret_cast<const float4*>(prm + kOffB2 + c * 32 + 4 * j);
+            const float4 bs = GM_PRM4(prm + kOffB2 + c * 32 + 4 * j);
             v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f);
             v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
             v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f);
@@ -491,7 +513,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
         float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
 #pragma unroll
         for (int j = 0; j < kH / 4; ++j) {
-          const float4 t = *reinterpret_cast<const float4*>(prm + kOffB3 + 4 * j);
+          const float4 t = GM_PRM4(prm + kOffB3 + 4 * j);
           x[4 * j] += t.x; x[4 * j + 1] += t.y; x[4 * j + 2] += t.z; x[4 * j + 3] += t.w;
           sa += x[4 * j]; sb += x[4 * j + 1]; sc += x[4 * j + 2]; sd += x[4 * j + 3];
         }
@@ -506,8 +528,8 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
         const float rstd = 1.0f / sqrtf(((qa + qb) + (qc + qd)) * (1.0f / kH) + 1e-5f);
 #pragma unroll
         for (int j = 0; j < kH / 4; ++j) {
-          const float4 g4 = *reinterpret_cast<const float4*>(prm + kOffG + 4 * j);
-          const float4 b4 = *reinterpret_cast<const float4*>(prm + kOffBeta + 4 * j);
+          const float4 g4 = GM_PRM4(prm + kOffG + 4 * j);
+          const float4 b4 = GM_PRM4(prm + kOffBeta + 4 * j);
           *reinterpret_cast<float4*>(S + (j >> 3) * kBoxBytes + ro[j & 7]) =
               make_float4(x[4 * j] * rstd * g4.x + b4.x, x[4 * j + 1] * rstd * g4.y + b4.y,
                           x[4 * j + 2] * rstd * g4.z + b4.z, x[4 * j + 3] * rstd * g4.w + b4.w);
@@ -608,7 +630,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       GM_ESTAMP(12);
       named_bar_sync(1 + s, kTile);            // every row has been read: the slot's staging tile is free
       GM_ESTAMP(13);
-      if (has_next) begin_tile(k + 2);
+      if (has_next) begin_tile(k + KSTEP);
       GM_ESTAMP(14);
     }
   }
@@ -730,7 +752,7 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
       auto e2_block = [&](int c, float* v) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float4 bs = *reinterpret_cast<const float4*>(prm + kOffB2 + c * 32 + 4 * j);
+          const float4 bs = GM_PRM4(prm + kOffB2 + c * 32 + 4 * j);
           v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f);
           v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
           v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f);
@@ -765,7 +787,7 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
       float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
 #pragma unroll
       for (int j = 0; j < kH / 4; ++j) {
-        const float4 t = *reinterpret_cast<const float4*>(prm + kOffB3 + 4 * j);
+        const float4 t = GM_PRM4(prm + kOffB3 + 4 * j);
         y[4 * j] += t.x; y[4 * j + 1] += t.y; y[4 * j + 2] += t.z; y[4 * j + 3] += t.w;
         sa += y[4 * j]; sb += y[4 * j + 1]; sc += y[4 * j + 2]; sd += y[4 * j + 3];
       }
@@ -780,8 +802,8 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
       const float rstd = 1.0f / sqrtf(((qa + qb) + (qc + qd)) * (1.0f / kH) + 1e-5f);
 #pragma unroll
       for (int j = 0; j < kH / 4; ++j) {
-        const float4 g4 = *reinterpret_cast<const float4*>(prm + kOffG + 4 * j);
-        const float4 b4 = *reinterpret_cast<const float4*>(prm + kOffBeta + 4 * j);
+        const float4 g4 = GM_PRM4(prm + kOffG + 4 * j);
+        const float4 b4 = GM_PRM4(prm + kOffBeta + 4 * j);
         *reinterpret_cast<float4*>(S + (j >> 3) * kBoxBytes + ro[j & 7]) =
             make_float4(y[4 * j] * rstd * g4.x + b4.x, y[4 * j + 1] * rstd * g4.y + b4.y,
                         y[4 * j + 2] * rstd * g4.z + b4.z, y[4 * j + 3] * rstd * g4.w + b4.w);
