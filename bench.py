@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--rollout-steps", type=int, default=300)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-c3", action="store_true", help="skip the 100k-particle roofline leg")
+    ap.add_argument("--no-c4", action="store_true", help="skip the CMA-ES population line (64 candidates x 150 steps)")
     ap.add_argument("--only-c3", action="store_true", help="profiling aid: only the 100k-particle forward profile")
     return ap.parse_args()
 
@@ -267,6 +268,7 @@ def run_ours(args):
         barrier()
     ms = sum(a.elapsed_time(b) for a, b in evs)
     final_dev = plan.obs[-1].clone()
+    launches = plan.launches_per_step * T * K + (gm._lib.launch_count() - l0)
 
     # ---- end to end through the public API with HOST buffers: `e2e` ----
     obs_host = obs.clone().pin_memory()
@@ -296,13 +298,37 @@ def run_ours(args):
     ms_e2e = sum(a.elapsed_time(b) for a, b in evs2)
     assert torch.equal(out_host, final_dev.cpu()), "e2e rollout must reproduce the device-resident rollout"
 
-    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    # ---- C4: CMA-ES population, 64 candidates x 150-step rollouts, population sharded over the ranks:
+    #      each rank batches its candidates as disjoint graphs in ONE plan; no collective on the data path ----
+    ms_c4, c4 = 0.0, None
+    if not args.no_c4:
+        from gnn_manip_b200.sharding import partition_population
+        pop, T4 = 64, 150
+        lo, hi = partition_population(pop, world, rank)
+        curves = [control_curve(T4, i) for i in range(lo, hi)]
+        rot4 = np.stack([c[0] for c in curves]); ty4 = np.stack([c[1] for c in curves])
+        del plan
+        plan4 = gm.Rollout(model, ga, obs, rot=rot4, ty=ty4, ty_init=tuple(scenes.TY_INIT), n_graphs=hi - lo,
+                           use_cuda_graph=True, impl=gm._lib.GM_IMPL_TC, device=dev)
+        plan4.run(3)                                               # warm-up (graph capture, caches)
+        barrier()
+        flush.add_(1.0)
+        plan4.reset()
+        a4, b4 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a4.record(stream)
+        plan4.run(T4)
+        b4.record(stream)
+        barrier()
+        ms_c4 = a4.elapsed_time(b4)
+        c4 = {"population": pop, "rollout_steps": T4, "candidates_per_rank": hi - lo, "particles": N}
+        del plan4
+
+    t = torch.tensor([ms, ms_e2e, ms_c4], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = float(t[0]), float(t[1])
+    ms, ms_e2e, ms_c4 = float(t[0]), float(t[1]), float(t[2])
     value = world * N * T * K / (ms * 1e-3)
     e2e = world * N * T * K / (ms_e2e * 1e-3)
-    launches = plan.launches_per_step * T * K + (gm._lib.launch_count() - l0)
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -315,6 +341,11 @@ def run_ours(args):
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches), "clocks": clocks.summary()}
 
+    if c4 is not None:
+        c4.update({"ms": ms_c4, "cma_candidates_per_s": c4["population"] / (ms_c4 * 1e-3),
+                   "particle_steps_per_s": c4["population"] * N * c4["rollout_steps"] / (ms_c4 * 1e-3),
+                   "us_per_rollout_step": 1e3 * ms_c4 / c4["rollout_steps"]})
+        line["c4_cma_population"] = c4
     if rank == 0:
         per, E, _ = profile_forward(gm, model, obs, reps=20, warm=3, flush=None)
         line["roofline"] = roofline_entry(per[2], E, pk, sustained=True)
