@@ -94,10 +94,6 @@ __device__ __forceinline__ void stage_rows32_gather(const uint32_t* db, const fl
 }
 
 __device__ __forceinline__ void red_add_v4(float* gdst, const float4& v) {
-#ifdef GM_EXP_STG   // timing experiment only (wrong results): plain store instead of the reduction
-  *reinterpret_cast<float4*>(gdst) = v;
-  return;
-#endif
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(gdst), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
                : "memory");
 }
@@ -246,11 +242,7 @@ __device__ unsigned long long g_edge_stamps[32];
 #endif
 
 constexpr int kOffB2 = 0, kOffB3 = 128, kOffG = 256, kOffBeta = 384;
-#ifdef GM_EXP_NOPRM
-#define GM_PRM4(ptr) make_float4(0.5f, 0.25f, 0.125f, 1.5f)
-#else
 #define GM_PRM4(ptr) (*reinterpret_cast<const float4*>(ptr))
-#endif
 
 }  // namespace
 
@@ -311,11 +303,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
   {
     // ---------------- compute warpgroups: slot s, thread = edge row r ----------------
     const int s = warp >> 2, q = warp & 3, r = tid & (kTile - 1), r0 = q * 32;
-#ifdef GM_EXP_ONESLOT   // timing experiment: slot 1 idle, slot 0 takes every tile
-    const int KSTEP = 1, K0 = s == 0 ? 0 : (1 << 30);
-#else
-    const int KSTEP = 2, K0 = s;
-#endif
+    const int KSTEP = 2, K0 = s;             // slot s takes this CTA's tiles s, s + 2, ...
     char* S = S_base + s * kStageBytes;
     const uint32_t S_s = smem_u32(S);
     uint32_t ro[8];                            // row-owner offsets of the 8 chunks of a box
@@ -471,13 +459,15 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       {
         float va[32], vb[32];
         auto e2_block = [&](int c, float* v) {
+          float4 bs[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bs[j] = GM_PRM4(prm + kOffB2 + c * 32 + 4 * j);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float4 bs = GM_PRM4(prm + kOffB2 + c * 32 + 4 * j);
-            v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f);
-            v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
-            v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f);
-            v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w, 0.f);
+            v[4 * j] = fmaxf(v[4 * j] + bs[j].x, 0.f);
+            v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs[j].y, 0.f);
+            v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs[j].z, 0.f);
+            v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs[j].w, 0.f);
           }
           put_operand32(v, tAH, tAL, c);
         };
@@ -510,14 +500,24 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
 #pragma unroll
         for (int c = 0; c < 4; ++c) tmem_ld32(tD + c * 32, x + c * 32);
         tmem_ld_wait();
+        GM_ESTAMP(25);
         float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
+        // parameters are fetched a whole 32-column box at a time (8 independent 128-bit loads in flight) so that
+        // their shared-memory latency is paid once per box, not once per 4 columns
 #pragma unroll
-        for (int j = 0; j < kH / 4; ++j) {
-          const float4 t = GM_PRM4(prm + kOffB3 + 4 * j);
-          x[4 * j] += t.x; x[4 * j + 1] += t.y; x[4 * j + 2] += t.z; x[4 * j + 3] += t.w;
-          sa += x[4 * j]; sb += x[4 * j + 1]; sc += x[4 * j + 2]; sd += x[4 * j + 3];
+        for (int c = 0; c < 4; ++c) {
+          float4 t[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) t[j] = GM_PRM4(prm + kOffB3 + c * 32 + 4 * j);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float* xx = x + c * 32 + 4 * j;
+            xx[0] += t[j].x; xx[1] += t[j].y; xx[2] += t[j].z; xx[3] += t[j].w;
+            sa += xx[0]; sb += xx[1]; sc += xx[2]; sd += xx[3];
+          }
         }
         const float mean = ((sa + sb) + (sc + sd)) * (1.0f / kH);
+        GM_ESTAMP(26);
         float qa = 0.f, qb = 0.f, qc = 0.f, qd = 0.f;
 #pragma unroll
         for (int j = 0; j < kH / 4; ++j) {
@@ -526,13 +526,22 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
           qc = fmaf(x[4 * j + 2], x[4 * j + 2], qc); qd = fmaf(x[4 * j + 3], x[4 * j + 3], qd);
         }
         const float rstd = 1.0f / sqrtf(((qa + qb) + (qc + qd)) * (1.0f / kH) + 1e-5f);
+        GM_ESTAMP(27);
 #pragma unroll
-        for (int j = 0; j < kH / 4; ++j) {
-          const float4 g4 = GM_PRM4(prm + kOffG + 4 * j);
-          const float4 b4 = GM_PRM4(prm + kOffBeta + 4 * j);
-          *reinterpret_cast<float4*>(S + (j >> 3) * kBoxBytes + ro[j & 7]) =
-              make_float4(x[4 * j] * rstd * g4.x + b4.x, x[4 * j + 1] * rstd * g4.y + b4.y,
-                          x[4 * j + 2] * rstd * g4.z + b4.z, x[4 * j + 3] * rstd * g4.w + b4.w);
+        for (int c = 0; c < 4; ++c) {
+          float4 g4[8], b4[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            g4[j] = GM_PRM4(prm + kOffG + c * 32 + 4 * j);
+            b4[j] = GM_PRM4(prm + kOffBeta + c * 32 + 4 * j);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float* xx = x + c * 32 + 4 * j;
+            *reinterpret_cast<float4*>(S + c * kBoxBytes + ro[j]) =
+                make_float4(xx[0] * rstd * g4[j].x + b4[j].x, xx[1] * rstd * g4[j].y + b4[j].y,
+                            xx[2] * rstd * g4[j].z + b4[j].z, xx[3] * rstd * g4[j].w + b4[j].w);
+          }
         }
       }
       __syncwarp();

@@ -16,5 +16,6 @@ print("kernel ms", per, "E", E)
 print("edge compute stamps (cycles since stamp 0):", [int(x - s[0]) for x in s[:16]])
 print("edge compute deltas:", [int(s[i + 1] - s[i]) for i in range(15)])
 print("edge E1 fine stamps (since stamp 5: ld0 done, blk0, blk1, blk2, blk3, published, issued):", [int(x - s[5]) for x in s[16:23]])
+print("edge LN fine stamps (since stamp 2: acc loaded, mean, rstd; stamp 10 = rows stored):", [int(x - s[2]) for x in (s[25], s[26], s[27], s[10])])
 print("edge pdl wait (cycles):", int(s[24] - s[23]))
 print("node stamps:", [int(x - s[32]) for x in s[32:44]])
