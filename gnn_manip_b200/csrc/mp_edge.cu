@@ -283,14 +283,6 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = sh->tmem_base;
-#ifdef GM_STAMPS
-  if (blockIdx.x == 0 && tid == 0) g_edge_stamps[23] = clock64();
-#endif
-  pdl_launch_dependents();
-  pdl_wait();
-#ifdef GM_STAMPS
-  if (blockIdx.x == 0 && tid == 0) g_edge_stamps[24] = clock64();
-#endif
                                  // everything above touched constant parameters only
 
   const int E = min(*g.n_edges_dev, g.max_edges);
@@ -380,10 +372,18 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     // weights of this CTA landed; peer barriers initialised, peer weights landed, TMEM of the pair allocated
     mbar_wait(smem_u32(&sh->w_full), 0);
     cluster_sync_all();
-    if (K0 < n_my) {
-      operand_from_stage();
-      begin_tile(K0);
-    }
+    if (K0 < n_my) operand_from_stage();
+    // Everything so far read only constants and e, which the kernel two launches back (the previous edge kernel /
+    // the edge encoder) finished writing before this grid could start; Pr / Ps come from the node kernel right before.
+#ifdef GM_STAMPS
+    if (blockIdx.x == 0 && tid == 0) g_edge_stamps[23] = clock64();
+#endif
+    pdl_wait();
+    pdl_launch_dependents();
+#ifdef GM_STAMPS
+    if (blockIdx.x == 0 && tid == 0) g_edge_stamps[24] = clock64();
+#endif
+    if (K0 < n_my) begin_tile(K0);
     for (int k = K0; k < n_my; k += KSTEP) {
       const int row0 = (blockIdx.x + k * grid) * kTile;
       const int rows_valid = min(kTile, E - row0);
@@ -692,8 +692,8 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = sh->tmem_base;
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
 
   const int E = min(*g.n_edges_dev, g.max_edges);
   const int n_tiles = (E + kTile - 1) / kTile;

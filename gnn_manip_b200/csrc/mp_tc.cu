@@ -532,8 +532,8 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
   constexpr int R = kTile / (NT / 32);
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
   if ((int)blockIdx.x < n_tiles) load_w(c, m.wc[0]);
-  pdl_launch_dependents();
-  pdl_wait();                                      // everything above reads constant parameters only
+  pdl_wait();                                      // upstream results are complete and visible from here on
+  pdl_launch_dependents();                         // (after the wait: a dependent may then rely on everything two kernels back)
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
@@ -634,8 +634,8 @@ enc_node_kernel(TcMlp m, TcMlp next, int node_dim, const float* __restrict__ nod
   __syncthreads();
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
   if ((int)blockIdx.x < n_tiles) load_w(c, m.wc[2]);
-  pdl_launch_dependents();
-  pdl_wait();
+  pdl_wait();                                      // upstream results are complete and visible from here on
+  pdl_launch_dependents();                         // (after the wait: a dependent may then rely on everything two kernels back)
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
@@ -687,8 +687,8 @@ enc_edge_kernel(TcMlp m, int edge_dim, const float* __restrict__ pos, int pos_st
   stage_params(c, m);
   for (int i = c.tid; i < kH * edge_dim; i += NT) c.misc->w1[i] = m.w1[i];
   __syncthreads();
-  pdl_launch_dependents();
-  pdl_wait();
+  pdl_wait();                                      // upstream results are complete and visible from here on
+  pdl_launch_dependents();                         // (after the wait: a dependent may then rely on everything two kernels back)
   const int E = min(*g.n_edges_dev, g.max_edges);
   const int n_tiles = (E + kTile - 1) / kTile;
   // this thread's input row of a tile: explicit edge_attr row, or the displacement features built from positions
