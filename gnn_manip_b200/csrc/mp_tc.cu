@@ -532,8 +532,6 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
   constexpr int R = kTile / (NT / 32);
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
   if ((int)blockIdx.x < n_tiles) load_w(c, m.wc[0]);
-  pdl_wait();                                      // upstream results are complete and visible from here on
-  pdl_launch_dependents();                         // (after the wait: a dependent may then rely on everything two kernels back)
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
@@ -541,6 +539,16 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
     const bool stamp_on = tile == (int)blockIdx.x;
 #endif
     GM_STAMP(32);
+    // node latents -> T (the second layer-1 operand).  v was written two kernels back (the previous node kernel), so
+    // the first tile's rows are fetched before this grid waits for the edge kernel that is still draining.
+    {
+      const float* v_in = b.v;
+      load_rows_to_a16(c, T, rows_valid, [=](int r) { return v_in + (size_t)(node0 + r) * kH; });
+    }
+    if (tile == (int)blockIdx.x) {
+      pdl_wait();                                  // aggpart / carry of this step's edge kernel are complete from here on
+      pdl_launch_dependents();
+    }
     // ---- prologue: total aggregate per node (first-tile partial + carries of the following agg tiles) -> A0,
     //      node latents -> T (as the second layer-1 operand) ----
     {
@@ -573,10 +581,6 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
         *reinterpret_cast<uint2*>(A0 + o) = hi;
         *reinterpret_cast<uint2*>(A0 + kImageBytes + o) = lo;
       }
-    }
-    {
-      const float* v_in = b.v;
-      load_rows_to_a16(c, T, rows_valid, [=](int r) { return v_in + (size_t)(node0 + r) * kH; });
     }
     // ---- layer 1: agg W1a^T + v W1b^T ----
     GM_STAMP(33);
@@ -614,6 +618,10 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
     node_finish(c, A0, T, prm, true, next, has_dec != 0, out_dim, pred, b, node0, rows_valid);
     GM_STAMP(42);
     if (tile + (int)gridDim.x < n_tiles) load_w(c, m.wc[0]);
+  }
+  if ((int)blockIdx.x >= n_tiles) {
+    pdl_wait();
+    pdl_launch_dependents();
   }
   ctx_fini(c, 128);
 }
