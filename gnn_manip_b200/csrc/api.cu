@@ -263,7 +263,9 @@ struct FwdProfile {
 int forward_tc(const gm_model* m, const float* nodes, const float* edge_attr, const float* pos, int pos_stride,
                float conn_r, int n_nodes, int max_edges, const int* n_edges_dev, const int* recv_ptr,
                const int* esend, const int* erecv, const int* eref, float* pred, const FwdWs& w,
-               cudaStream_t st, FwdProfile* prof = nullptr) {
+               cudaStream_t st, FwdProfile* prof = nullptr, cudaEvent_t enc_node_done = nullptr) {
+  // enc_node_done: the caller already launched the node encoder on another stream (it needs only the node features,
+  // so a rollout runs it beside the graph build); the first edge step joins on the event instead.
   GM_REQUIRE(m->tc_ok, "model shape (hidden=%d, num_layers=%d) is not covered by the tcgen05 kernels", m->hidden,
              m->num_layers);
   TcGraph g{n_edges_dev, max_edges, n_nodes, esend, erecv, recv_ptr};
@@ -273,10 +275,15 @@ int forward_tc(const gm_model* m, const float* nodes, const float* edge_attr, co
   GM_MARK(0);
   if ((rc = tc_enc_edge(m->tc_enc_edge, m->edge_dim, pos, pos_stride, conn_r, edge_attr, eref, g, b, st))) return rc;
   GM_MARK(1);
-  if ((rc = tc_enc_node(m->tc_enc_node, m->tc_proc_edge[0], m->node_dim, nodes, g, b, st))) return rc;
+  if (enc_node_done == nullptr) {
+    if ((rc = tc_enc_node(m->tc_enc_node, m->tc_proc_edge[0], m->node_dim, nodes, g, b, st))) return rc;
+  } else {
+    GM_CUDA(cudaStreamWaitEvent(st, enc_node_done, 0));
+  }
   for (int s = 0; s < m->m_steps; ++s) {
     GM_MARK(2);
-    if ((rc = tc_mp_edge(m->tc_proc_edge[s], g, b, st))) return rc;
+    // after a join the first edge step is an ordinary launch: e then comes from the kernel right before it
+    if ((rc = tc_mp_edge(m->tc_proc_edge[s], g, b, st, !(s == 0 && enc_node_done != nullptr)))) return rc;
     GM_MARK(3);
     const bool last = s + 1 == m->m_steps;
     if ((rc = tc_mp_node(m->tc_proc_node[s], last ? nullptr : &m->tc_proc_edge[s + 1], last ? &m->tc_dec : nullptr,
@@ -304,6 +311,8 @@ struct gm_rollout {
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
   int64_t launches_per_step = 0;
+  cudaStream_t side = nullptr;            // node encoder runs here, beside the graph build
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 namespace gm {
@@ -340,13 +349,24 @@ int rollout_step(gm_rollout* r, cudaStream_t st) {
   if ((rc = apply_control(d.obs, r->rp, st))) return rc;
   const float* last = d.obs + (size_t)(d.k - 1) * r->n * d.D;
   const float* pos = last + p.cart[0];
+  if ((rc = node_features(d.obs, d.k, r->n, d.D, p, r->nodes, st))) return rc;
+  const bool fork = r->tc && r->side != nullptr;
+  if (fork) {
+    // the node encoder needs the node features only: fork it onto the side stream so that it overlaps the
+    // (many small) graph-build kernels; forward_tc joins before the first edge step
+    TcGraph g{r->n_edges, r->max_edges, r->n, r->esend, r->erecv, r->recv_ptr};
+    TcBuffers b{r->fws.e, r->fws.v, r->fws.pr, r->fws.ps, r->fws.aggpart, r->fws.carry};
+    GM_CUDA(cudaEventRecord(r->ev_fork, st));
+    GM_CUDA(cudaStreamWaitEvent(r->side, r->ev_fork, 0));
+    if ((rc = tc_enc_node(m->tc_enc_node, m->tc_proc_edge[0], m->node_dim, r->nodes, g, b, r->side))) return rc;
+    GM_CUDA(cudaEventRecord(r->ev_join, r->side));
+  }
   if ((rc = radius_graph(pos, d.D, d.n_per_graph, d.n_graphs, d.phys.conn_r, d.max_neighbours, r->nbr, r->cnt,
                          r->edge_ptr, r->recv_ptr, r->esend, r->erecv, r->eref, r->n_edges, r->gws, st)))
     return rc;
-  if ((rc = node_features(d.obs, d.k, r->n, d.D, p, r->nodes, st))) return rc;
   if (r->tc)
     rc = forward_tc(m, r->nodes, nullptr, pos, d.D, p.conn_r, r->n, r->max_edges, r->n_edges, r->recv_ptr, r->esend,
-                    r->erecv, r->eref, r->pred, r->fws, st);
+                    r->erecv, r->eref, r->pred, r->fws, st, nullptr, fork ? r->ev_join : nullptr);
   else
     rc = forward_simt(m, r->nodes, nullptr, pos, d.D, p.conn_r, r->n, r->max_edges, r->n_edges, r->recv_ptr,
                       r->esend, r->erecv, r->eref, r->pred, r->fws, st);
@@ -724,6 +744,12 @@ int gm_rollout_create(gm_rollout** plan, const gm_rollout_desc* d, void* workspa
     rigid_slot_kernel<<<ceil_div(d->n_rigid, 128), 128, 0, st>>>(d->rigid_idx, d->n_rigid, const_cast<int*>(rp.rigid_slot));
 
   int rc = GM_OK;
+  if (r->tc) {
+    ce = cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&r->ev_join, cudaEventDisableTiming);
+    if (ce != cudaSuccess) { gm_rollout_destroy(r); return cuda_fail(ce, "rollout side stream"); }
+  }
   if (d->use_cuda_graph) {
     // capture one rollout step on a private stream; replays are ordered on the caller's stream
     cudaStream_t cs;
@@ -790,6 +816,9 @@ void gm_rollout_destroy(gm_rollout* r) {
   if (!r) return;
   if (r->exec) cudaGraphExecDestroy(r->exec);
   if (r->graph) cudaGraphDestroy(r->graph);
+  if (r->ev_fork) cudaEventDestroy(r->ev_fork);
+  if (r->ev_join) cudaEventDestroy(r->ev_join);
+  if (r->side) cudaStreamDestroy(r->side);
   delete r;
 }
 

@@ -75,8 +75,8 @@ struct Arena {
 // Launch with programmatic stream serialization (and an optional cluster width): the kernel may start while its
 // predecessor in the stream drains; it calls pdl_wait() before touching upstream data.
 template <typename... KArgs, typename... Args>
-static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t stream,
-                                     int cluster_x, Args... args) {
+static inline cudaError_t launch_ex(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t stream,
+                                    int cluster_x, bool programmatic, Args... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(block);
@@ -84,9 +84,11 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int blo
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   int n = 0;
-  attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[n].val.programmaticStreamSerializationAllowed = 1;
-  ++n;
+  if (programmatic) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
   if (cluster_x > 1) {
     attr[n].id = cudaLaunchAttributeClusterDimension;
     attr[n].val.clusterDim.x = cluster_x;
@@ -97,6 +99,11 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int blo
   cfg.attrs = attr;
   cfg.numAttrs = n;
   return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t stream,
+                                     int cluster_x, Args... args) {
+  return launch_ex(kernel, grid, block, smem, stream, cluster_x, true, args...);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -938,13 +938,15 @@ int tc_configure_edge() {
   return GM_OK;
 }
 
-int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_t stream) {
+int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_t stream, bool programmatic) {
   if (g.max_edges <= 0) return GM_OK;
   int rc = tc_configure_edge();
   if (rc) return rc;
   // CTA pairs (clusters of 2): even grid, at most one CTA per SM
   const int grid = min((ceil_div(g.max_edges, kTile) + 1) & ~1, kNumSMs & ~1);
-  GM_CUDA(launch_pdl(mp_edge_kernel, grid, kNTE, (size_t)kEdgeSmemBytes, stream, 2, m, g, b));
+  // programmatic = false: fully ordered after everything before it in the stream (its early part reads e, which
+  // must then come from the kernel right before it or from a joined stream)
+  GM_CUDA(launch_ex(mp_edge_kernel, grid, kNTE, (size_t)kEdgeSmemBytes, stream, 2, programmatic, m, g, b));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("mp_edge_kernel");
   return GM_OK;

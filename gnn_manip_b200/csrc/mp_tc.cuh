@@ -55,7 +55,7 @@ int tc_enc_edge_pair(const TcMlp& m, const float* pos, int pos_stride, float con
                      const TcBuffers& b, cudaStream_t stream);
 int tc_enc_node(const TcMlp& m, const TcMlp& next_edge, int node_dim, const float* nodes, const TcGraph& g,
                 const TcBuffers& b, cudaStream_t stream);
-int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_t stream);
+int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_t stream, bool programmatic = true);
 // next_edge: the following step's edge MLP (for pr/ps) or, when dec != null, the decoder.
 int tc_mp_node(const TcMlp& m, const TcMlp* next_edge, const TcMlp* dec, int out_dim, float* pred,
                const TcGraph& g, const TcBuffers& b, cudaStream_t stream);
