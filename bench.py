@@ -357,6 +357,14 @@ def run_ours(args):
             obs3, _ = scenes.make_state(100_000, seed=0, n_rigid=0)
             per3, E3, _ = profile_forward(gm, model, obs3, reps=5, warm=2, flush=flush)
             line["roofline_c3"] = roofline_entry(per3[2], E3, pk, sustained=True)
+            try:   # DRAM bytes of the same launch from the committed ncu capture (never measured under this run)
+                with open(os.path.join(ROOT, "profiles", "mp_edge_traffic.json")) as f:
+                    tr = json.load(f)["c3"]
+                if int(tr["edges_per_launch"]) == int(E3):
+                    line["roofline_c3"]["traffic"] = tr["dram_bytes_per_launch"]
+                    line["roofline_c3"]["traffic_source"] = tr["source"]
+            except (OSError, KeyError, ValueError):
+                pass
             line["kernel_us_c3"] = {"enc_edge": 1e3 * per3[0], "enc_node": 1e3 * per3[1], "mp_edge": 1e3 * per3[2],
                                     "mp_node": 1e3 * per3[3]}
             fwd_ms = per3[0] + per3[1] + 10 * (per3[2] + per3[3])
