@@ -383,7 +383,14 @@ def run_ours(args):
 
 if __name__ == "__main__":
     a = parse_args()
+    # stdout carries exactly ONE JSON line: anything native libraries write to fd 1 meanwhile (NCCL prints its version
+    # banner there on some boxes, make prints when it rebuilds the oracle) is sent to stderr instead
+    sys.stdout.flush()
+    _real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(_real_stdout, "w")
     if a.impl == "reference":
         run_reference(a)
     else:
         run_ours(a)
+    sys.stdout.flush()

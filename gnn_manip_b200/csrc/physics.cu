@@ -18,6 +18,8 @@ namespace {
 
 __global__ void node_features_kernel(const float* __restrict__ obs, int k, int n, int D, PhysParams p,
                                      float* __restrict__ nodes) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   const int F = p.node_dim;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)n * F) return;
@@ -79,6 +81,8 @@ __device__ __forceinline__ void rigid_target(const RolloutParams& rp, int g, int
 
 // Step (1) of the loop body: control columns of the rigid particles (traj_utils.py:126-135).
 __global__ void apply_control_kernel(float* __restrict__ obs, RolloutParams rp) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= rp.n_graphs * rp.n_rigid) return;
   const int g = idx / rp.n_rigid, r = idx - g * rp.n_rigid;
@@ -104,6 +108,8 @@ __global__ void apply_control_kernel(float* __restrict__ obs, RolloutParams rp) 
 // traj_utils.py:146-152). One thread per node; each node's rows are private to its thread.
 __global__ void integrate_kernel(float* __restrict__ obs, const float* __restrict__ pred, RolloutParams rp,
                                  float* __restrict__ next_pos_out) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   const int node = blockIdx.x * blockDim.x + threadIdx.x;
   const int n = rp.n_graphs * rp.n_per_graph;
   if (node >= n) return;
@@ -150,6 +156,8 @@ __global__ void integrate_kernel(float* __restrict__ obs, const float* __restric
 }
 
 __global__ void bump_step_kernel(int* step_dev) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   if (threadIdx.x == 0 && blockIdx.x == 0) *step_dev += 1;
 }
 
@@ -158,7 +166,7 @@ __global__ void bump_step_kernel(int* step_dev) {
 int node_features(const float* obs, int k, int n, int D, const PhysParams& p, float* nodes, cudaStream_t stream) {
   GM_REQUIRE(k >= 2 && n > 0 && D > 0, "node_features: bad shape k=%d n=%d D=%d", k, n, D);
   const long long total = (long long)n * p.node_dim;
-  node_features_kernel<<<ceil_div(total, 256), 256, 0, stream>>>(obs, k, n, D, p, nodes);
+  GM_CUDA(launch_pdl(node_features_kernel, (int)ceil_div(total, 256), 256, 0, stream, 1, obs, k, n, D, p, nodes));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("node_features_kernel");
   return GM_OK;
@@ -177,7 +185,7 @@ int edge_features(const float* pos, int stride, const int* send, const int* recv
 int apply_control(float* obs, const RolloutParams& rp, cudaStream_t stream) {
   const int total = rp.n_graphs * rp.n_rigid;
   if (total <= 0) return GM_OK;
-  apply_control_kernel<<<ceil_div(total, 128), 128, 0, stream>>>(obs, rp);
+  GM_CUDA(launch_pdl(apply_control_kernel, (int)ceil_div(total, 128), 128, 0, stream, 1, obs, rp));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("apply_control_kernel");
   return GM_OK;
@@ -185,8 +193,8 @@ int apply_control(float* obs, const RolloutParams& rp, cudaStream_t stream) {
 
 int integrate(float* obs, const float* pred, const RolloutParams& rp, float* next_pos_out, cudaStream_t stream) {
   const int n = rp.n_graphs * rp.n_per_graph;
-  integrate_kernel<<<ceil_div(n, 128), 128, 0, stream>>>(obs, pred, rp, next_pos_out);
-  bump_step_kernel<<<1, 32, 0, stream>>>(rp.step_dev);
+  GM_CUDA(launch_pdl(integrate_kernel, ceil_div(n, 128), 128, 0, stream, 1, obs, pred, rp, next_pos_out));
+  GM_CUDA(launch_pdl(bump_step_kernel, 1, 32, 0, stream, 1, rp.step_dev));
   GM_LAUNCHED(2);
   GM_LAUNCH_CHECK("integrate_kernel");
   return GM_OK;

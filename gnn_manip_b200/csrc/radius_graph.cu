@@ -118,6 +118,8 @@ __device__ void grid_setup_body(const unsigned* bbox, double r, int n_graphs, in
 __global__ void __launch_bounds__(1024)
 prepare_small_kernel(const float* __restrict__ pos, int stride, int n, double r, int n_graphs, int max_cells,
                      GridParams* __restrict__ gp, int* __restrict__ cell_cnt, int* __restrict__ indeg_fill /*2(n+1)*/) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   __shared__ unsigned s_box[6];
   if (threadIdx.x < 3) s_box[threadIdx.x] = 0xFFFFFFFFu;
   else if (threadIdx.x < 6) s_box[threadIdx.x] = 0u;
@@ -165,6 +167,8 @@ __device__ __forceinline__ void cell_coords(const GridParams& gp, float x, float
 __global__ void cell_count_kernel(const float* __restrict__ pos, int stride, int n, int n_per_graph,
                                   const GridParams* __restrict__ gpp, int* __restrict__ cell_of,
                                   int* __restrict__ cell_cnt) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const GridParams gp = *gpp;
@@ -181,6 +185,8 @@ __global__ void cell_count_kernel(const float* __restrict__ pos, int stride, int
 __global__ void cell_fill_kernel(const float* __restrict__ pos, int stride, int n,
                                  const int* __restrict__ cell_of, const int* __restrict__ cell_start,
                                  int* __restrict__ cell_cnt, float4* __restrict__ sorted) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   int cell = cell_of[i];
@@ -223,6 +229,8 @@ __global__ void __launch_bounds__(kNbrWarps * 32)
 neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                  const GridParams* __restrict__ gpp, int n, int n_per_graph, double r2, int K,
                  int* __restrict__ nbr, int* __restrict__ cnt_out, int* __restrict__ indeg) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   __shared__ double s_bd[kNbrWarps][kNbrBuf];
   __shared__ int s_bj[kNbrWarps][kNbrBuf];
   __shared__ double s_td[kNbrWarps][kMaxK];
@@ -303,6 +311,8 @@ __global__ void indeg_count_kernel(const int* __restrict__ recv_of_slot, long lo
 __global__ void recv_fill_kernel(const int* __restrict__ recv_of_slot, long long n_slots,
                                  const int* __restrict__ n_valid_dev, const int* __restrict__ recv_ptr,
                                  int* __restrict__ fill, int* __restrict__ keys) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n_slots) return;
   if (n_valid_dev && s >= *n_valid_dev) return;
@@ -370,6 +380,8 @@ __global__ void __launch_bounds__(256)
 recv_sort_emit_warp_kernel(const int* __restrict__ recv_ptr, int n, const int* __restrict__ keys, int K,
                            const int* __restrict__ edge_ptr, const int* __restrict__ send_of_slot,
                            int* __restrict__ esend, int* __restrict__ erecv, int* __restrict__ eref) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (j >= n) return;
@@ -467,12 +479,13 @@ int build_recv_csr(const int* recv_of_slot, long long n_slots, const int* n_vali
   int rc = exclusive_scan_i32(indeg, recv_ptr, n_nodes, scan_ws, stream);
   if (rc) return rc;
   if (n_slots > 0) {
-    recv_fill_kernel<<<ceil_div(n_slots, T), T, 0, stream>>>(recv_of_slot, n_slots, n_valid_dev, recv_ptr, fill, keys);
+    GM_CUDA(launch_pdl(recv_fill_kernel, (int)ceil_div(n_slots, T), T, 0, stream, 1, recv_of_slot, n_slots, n_valid_dev, recv_ptr,
+                       fill, keys));
     GM_LAUNCHED(1);
   }
   if (n_nodes > 0) {
-    recv_sort_emit_warp_kernel<<<ceil_div(n_nodes, 8), 256, 0, stream>>>(recv_ptr, n_nodes, keys, K, edge_ptr,
-                                                                        send_of_slot, esend, erecv, eref);
+    GM_CUDA(launch_pdl(recv_sort_emit_warp_kernel, ceil_div(n_nodes, 8), 256, 0, stream, 1, recv_ptr, n_nodes, keys, K, edge_ptr,
+                       send_of_slot, esend, erecv, eref));
     GM_LAUNCHED(1);
   }
   GM_LAUNCH_CHECK("build_recv_csr");
@@ -494,7 +507,8 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
 
   const bool small = n <= kSmallN;
   if (small) {
-    prepare_small_kernel<<<1, 1024, 0, stream>>>(pos, pos_stride, n, r, n_graphs, ws.max_cells, gp, ws.cell_cnt, ws.indeg);
+    GM_CUDA(launch_pdl(prepare_small_kernel, 1, 1024, 0, stream, 1, pos, pos_stride, n, r, n_graphs, ws.max_cells, gp, ws.cell_cnt,
+                       ws.indeg));
     GM_LAUNCHED(1);
   } else {
     bbox_init_kernel<<<1, 32, 0, stream>>>(ws.bbox);
@@ -504,13 +518,14 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
     GM_CUDA(cudaMemsetAsync(ws.indeg, 0, sizeof(int) * ((size_t)n + 1), stream));
     GM_LAUNCHED(3);
   }
-  cell_count_kernel<<<ceil_div(n, T), T, 0, stream>>>(pos, pos_stride, n, n_per_graph, gp, ws.cell_of, ws.cell_cnt);
+  GM_CUDA(launch_pdl(cell_count_kernel, ceil_div(n, T), T, 0, stream, 1, pos, pos_stride, n, n_per_graph, gp, ws.cell_of,
+                     ws.cell_cnt));
   int rc = exclusive_scan_i32(ws.cell_cnt, ws.cell_start, ws.max_cells, ws.scan_ws, stream);
   if (rc) return rc;
-  cell_fill_kernel<<<ceil_div(n, T), T, 0, stream>>>(pos, pos_stride, n, ws.cell_of, ws.cell_start, ws.cell_cnt,
-                                                     ws.sorted);
-  neighbour_kernel<<<ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream>>>(
-      ws.sorted, ws.cell_start, gp, n, n_per_graph, r * r, K, nbr, cnt, ws.indeg);
+  GM_CUDA(launch_pdl(cell_fill_kernel, ceil_div(n, T), T, 0, stream, 1, pos, pos_stride, n, ws.cell_of, ws.cell_start,
+                     ws.cell_cnt, ws.sorted));
+  GM_CUDA(launch_pdl(neighbour_kernel, ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream, 1, ws.sorted, ws.cell_start, gp, n,
+                     n_per_graph, r * r, K, nbr, cnt, ws.indeg));
   GM_LAUNCHED(3);
   GM_LAUNCH_CHECK("radius_graph kernels");
   rc = exclusive_scan_i32(cnt, edge_ptr, n, ws.scan_ws, stream, n_edges);

@@ -103,6 +103,8 @@ static __global__ void scan_apply_kernel(const int* __restrict__ in, long long n
 constexpr long long kScanSingleBlockMax = 1 << 14;
 static __global__ void scan_single_block_kernel(const int* __restrict__ in, long long n, int* __restrict__ out,
                                                 int* __restrict__ total_out) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
   __shared__ int sm[9];
   int carry = 0;
   for (long long base0 = 0; base0 < n; base0 += kScanTile) {
@@ -142,7 +144,7 @@ static __global__ void scan_copy_total_kernel(const int* __restrict__ out, long 
 inline int exclusive_scan_i32(const int* in, int* out, long long n, int* ws, cudaStream_t stream,
                               int* total_out = nullptr) {
   if (n <= kScanSingleBlockMax) {
-    scan_single_block_kernel<<<1, kScanThreads, 0, stream>>>(in, n, out, total_out);
+    GM_CUDA(launch_pdl(scan_single_block_kernel, 1, kScanThreads, 0, stream, 1, in, n, out, total_out));
     GM_LAUNCHED(1);
     GM_LAUNCH_CHECK("scan_single_block_kernel");
     return GM_OK;
