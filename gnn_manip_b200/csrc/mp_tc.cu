@@ -531,7 +531,7 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
   if (has_dec) stage_dec_params(c, next, out_dim);
   constexpr int R = kTile / (NT / 32);
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
-  if ((int)blockIdx.x < n_tiles) load_w(c, m.wc[0]);
+  if ((int)blockIdx.x < n_tiles) load_w(c, m.wc[1]);
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
@@ -545,6 +545,11 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
       const float* v_in = b.v;
       load_rows_to_a16(c, T, rows_valid, [=](int r) { return v_in + (size_t)(node0 + r) * kH; });
     }
+    // layer 1, node part first: D = v W1b^T needs nothing from this step's edge kernel, so for the first tile it runs
+    // (weights, operand and MMAs) while that kernel is still draining; the aggregated-edge part accumulates on top
+    launch_gemm(c, 1, 1, false);                   // sub 0 of launch_gemm(c, 1, ...) reads A buffer 1 (= T), TMEM cols 0
+    wait_gemm(c, 0);
+    load_w(c, m.wc[0]);
     if (tile == (int)blockIdx.x) {
       pdl_wait();                                  // aggpart / carry of this step's edge kernel are complete from here on
       pdl_launch_dependents();
@@ -582,16 +587,13 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
         *reinterpret_cast<uint2*>(A0 + kImageBytes + o) = lo;
       }
     }
-    // ---- layer 1: agg W1a^T + v W1b^T ----
+    // ---- layer 1, second part: D += agg W1a^T ----
     GM_STAMP(33);
-    launch_gemm(c, 0, 1, false);
+    launch_gemm(c, 0, 1, true);
     GM_STAMP(34);
     wait_gemm(c, 0);
     GM_STAMP(35);
-    load_w(c, m.wc[1]);
-    launch_gemm(c, 1, 1, true);
-    GM_STAMP(36);                    // sub 0 of launch_gemm(c, 1, ...) reads A buffer 1 (= T), TMEM cols 0
-    wait_gemm(c, 0);
+    GM_STAMP(36);
     load_w(c, m.wc[2]);
     {                                              // T is free: the fp32 residual rows travel into it meanwhile
       const float* v_in = b.v;
@@ -617,7 +619,7 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
     GM_STAMP(41);
     node_finish(c, A0, T, prm, true, next, has_dec != 0, out_dim, pred, b, node0, rows_valid);
     GM_STAMP(42);
-    if (tile + (int)gridDim.x < n_tiles) load_w(c, m.wc[0]);
+    if (tile + (int)gridDim.x < n_tiles) load_w(c, m.wc[1]);
   }
   if ((int)blockIdx.x >= n_tiles) {
     pdl_wait();
