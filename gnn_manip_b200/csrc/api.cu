@@ -112,6 +112,15 @@ size_t mlp_weight_count(int in1, int hidden, int out, int num_layers) {
 
 using namespace gm;
 
+#ifdef GM_TRACE
+namespace gm {
+int trace_dump_physics(unsigned long long*, int);
+int trace_dump_radius(unsigned long long*, int);
+int trace_dump_tc(unsigned long long*, int);
+int trace_dump_edge(unsigned long long*, int);
+}
+#endif
+
 struct gm_model {
   int node_dim, edge_dim, out_dim, hidden, num_layers, m_steps;
   size_t n_params;
@@ -822,7 +831,18 @@ void gm_rollout_destroy(gm_rollout* r) {
   delete r;
 }
 
+#ifdef GM_TRACE
+// -DGM_TRACE: four sections of 1 + 160 entries (count, then the %globaltimer stamps): physics, radius_graph, mp_tc, mp_edge
+int gm_debug_stamps(unsigned long long* out_host, int32_t n) {
+  if (n < 4 * 161) return GM_ERR_UNSUPPORTED;
+  cudaDeviceSynchronize();
+  int (*fn[4])(unsigned long long*, int) = {gm::trace_dump_physics, gm::trace_dump_radius, gm::trace_dump_tc, gm::trace_dump_edge};
+  for (int i = 0; i < 4; ++i) out_host[i * 161] = (unsigned long long)fn[i](out_host + i * 161 + 1, 160);
+  return GM_OK;
+}
+#else
 int gm_debug_stamps(unsigned long long* out_host, int32_t n) { return tc_debug_stamps(out_host, n); }
+#endif
 
 int gm_selftest_gemm(const float* x, const float* w, void* chunk, float* out, int32_t M, void* stream) {
   int rc = tc_configure();

@@ -240,7 +240,35 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 // prologue (barrier init, TMEM allocation, parameter / weight staging -- constant data only) overlaps the tail of
 // the previous kernel.  pdl_wait() must precede the first access to anything an earlier kernel of the stream wrote.
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#ifdef GM_TRACE
+// Debug aid (-DGM_TRACE): thread 0 of CTA 0 of every kernel records %globaltimer right after its dependency wait,
+// i.e. when its predecessor completed; one buffer per translation unit, read (and reset) by gm_debug_stamps().
+constexpr int kTraceCap = 160;
+static __device__ unsigned long long g_trace_t[kTraceCap];
+static __device__ unsigned int g_trace_n;
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    const unsigned i = atomicAdd(&g_trace_n, 1u);
+    if (i < kTraceCap) g_trace_t[i] = t;
+  }
+}
+#define GM_TRACE_DUMP(fn)                                                        \
+  int fn(unsigned long long* out, int cap) {                                     \
+    unsigned n = 0, z = 0;                                                       \
+    cudaMemcpyFromSymbol(&n, g_trace_n, sizeof(n));                              \
+    if (n > (unsigned)kTraceCap) n = kTraceCap;                                  \
+    if ((int)n > cap) n = (unsigned)cap;                                         \
+    if (n) cudaMemcpyFromSymbol(out, g_trace_t, sizeof(unsigned long long) * n); \
+    cudaMemcpyToSymbol(g_trace_n, &z, sizeof(z));                                \
+    return (int)n;                                                               \
+  }
+#else
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#define GM_TRACE_DUMP(fn)
+#endif
 
 // ---- bf16 hi/lo split of an fp32 pair: x ~= hi + lo with |err| <~ 2^-17 |x| ----
 __device__ __forceinline__ void split_bf16x2(float a, float b, uint32_t& hi, uint32_t& lo) {

@@ -976,4 +976,6 @@ int tc_selftest_gemm_ts(const float* x, const void* chunk, float* out, int M, cu
   return GM_OK;
 }
 
+GM_TRACE_DUMP(trace_dump_edge)
+
 }  // namespace gm

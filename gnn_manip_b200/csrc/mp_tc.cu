@@ -896,4 +896,6 @@ int tc_selftest_gemm(const float* x, const void* chunk, float* out, int M, cudaS
   return GM_OK;
 }
 
+GM_TRACE_DUMP(trace_dump_tc)
+
 }  // namespace gm

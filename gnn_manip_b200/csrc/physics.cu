@@ -200,4 +200,6 @@ int integrate(float* obs, const float* pred, const RolloutParams& rp, float* nex
   return GM_OK;
 }
 
+GM_TRACE_DUMP(trace_dump_physics)
+
 }  // namespace gm

@@ -203,26 +203,42 @@ __device__ __forceinline__ bool key_less(double da, int ja, double db, int jb) {
   return da < db || (da == db && ja < jb);
 }
 
-// Keep the `keep` smallest (d2, j) keys of buf[0..cnt) in sorted order at the front of buf.
-__device__ __forceinline__ void warp_select_smallest(double* bd, int* bj, double* td, int* tj, int cnt, int keep,
-                                                     int lane) {
-  for (int e = lane; e < cnt; e += 32) {
-    const double de = bd[e];
-    const int je = bj[e];
-    int rank = 0;
-    for (int o = 0; o < cnt; ++o) rank += key_less(bd[o], bj[o], de, je) ? 1 : 0;
-    if (rank < keep) {
-      td[rank] = de;
-      tj[rank] = je;
+// The `keep` smallest (d2, j) keys of buf[0..cnt), cnt <= kNbrBuf, in ascending order: each lane holds up to
+// kNbrBuf / 32 candidates in registers; `keep` rounds of a warp-wide arg-min (keys are unique: j is).  Round r's
+// winner is returned in lane r % 32 (slot r / 32 of out_d / out_j).
+constexpr int kNbrPerLane = kNbrBuf / 32;
+__device__ __forceinline__ int warp_select_smallest(const double* bd, const int* bj, int cnt, int keep, int lane,
+                                                    double* out_d, int* out_j) {
+  double d[kNbrPerLane];
+  int j[kNbrPerLane];
+#pragma unroll
+  for (int i = 0; i < kNbrPerLane; ++i) {
+    const int e = lane + 32 * i;
+    d[i] = e < cnt ? bd[e] : 1e300;
+    j[i] = e < cnt ? bj[e] : 0x7fffffff;
+  }
+  const int m = cnt < keep ? cnt : keep;
+  for (int r = 0; r < m; ++r) {
+    double bdv = d[0];
+    int bjv = j[0];
+#pragma unroll
+    for (int i = 1; i < kNbrPerLane; ++i)
+      if (key_less(d[i], j[i], bdv, bjv)) { bdv = d[i]; bjv = j[i]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double od = __shfl_xor_sync(0xffffffffu, bdv, o);
+      const int oj = __shfl_xor_sync(0xffffffffu, bjv, o);
+      if (key_less(od, oj, bdv, bjv)) { bdv = od; bjv = oj; }
+    }
+#pragma unroll
+    for (int i = 0; i < kNbrPerLane; ++i)
+      if (j[i] == bjv) { d[i] = 1e300; j[i] = 0x7fffffff; }
+    if (lane == (r & 31)) {
+      if (r < 32) { out_d[0] = bdv; out_j[0] = bjv; }
+      else { out_d[1] = bdv; out_j[1] = bjv; }
     }
   }
-  __syncwarp();
-  const int m = cnt < keep ? cnt : keep;
-  for (int e = lane; e < m; e += 32) {
-    bd[e] = td[e];
-    bj[e] = tj[e];
-  }
-  __syncwarp();
+  return m;
 }
 
 __global__ void __launch_bounds__(kNbrWarps * 32)
@@ -233,16 +249,12 @@ neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
   pdl_launch_dependents();
   __shared__ double s_bd[kNbrWarps][kNbrBuf];
   __shared__ int s_bj[kNbrWarps][kNbrBuf];
-  __shared__ double s_td[kNbrWarps][kMaxK];
-  __shared__ int s_tj[kNbrWarps][kMaxK];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int q = blockIdx.x * kNbrWarps + w;  // query in cell-sorted order (neighbouring warps share cells)
   if (q >= n) return;
   const GridParams gp = *gpp;
   double* bd = s_bd[w];
   int* bj = s_bj[w];
-  double* td = s_td[w];
-  int* tj = s_tj[w];
 
   const float4 me = sorted[q];
   const int qi = __float_as_int(me.w);
@@ -251,49 +263,81 @@ neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
   cell_coords(gp, me.x, me.y, me.z, c);
   const int gbase = (qi / n_per_graph) * gp.cells_per_graph;
 
-  int count = 0;
-  for (int dz = -1; dz <= 1; ++dz) {
-    const int z = c[2] + dz;
-    if (z < 0 || z >= gp.dim[2]) continue;
-    for (int dy = -1; dy <= 1; ++dy) {
-      const int y = c[1] + dy;
-      if (y < 0 || y >= gp.dim[1]) continue;
+  // The 27 neighbouring cells are 9 contiguous runs of the cell-sorted array (3 cells along x each): lane l < 9
+  // fetches run l; the runs are then walked as ONE flattened candidate list, 32 candidates per step, with the
+  // next step's positions already in flight while the current ones are tested.
+  int beg = 0, len = 0;
+  if (lane < 9) {
+    const int z = c[2] + lane / 3 - 1, y = c[1] + lane % 3 - 1;
+    if (z >= 0 && z < gp.dim[2] && y >= 0 && y < gp.dim[1]) {
       const int x0 = max(c[0] - 1, 0), x1 = min(c[0] + 1, gp.dim[0] - 1);
       const int row = gbase + (z * gp.dim[1] + y) * gp.dim[0];
-      const int beg = cell_start[row + x0], end = cell_start[row + x1 + 1];
-      for (int s0 = beg; s0 < end; s0 += 32) {
-        const int s = s0 + lane;
-        bool in = false;
-        double d2 = 0.0;
-        int j = -1;
-        if (s < end) {
-          const float4 o = sorted[s];
-          const double dx = px - (double)o.x, dyy = py - (double)o.y, dzz = pz - (double)o.z;
-          d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dyy, dyy)), __dmul_rn(dzz, dzz));
-          in = d2 <= r2;
-          j = __float_as_int(o.w);
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, in);
-        if (in) {
-          const int at = count + __popc(m & ((1u << lane) - 1u));
-          bd[at] = d2;
-          bj[at] = j;
-        }
-        count += __popc(m);
-        __syncwarp();
-        if (count + 32 > kNbrBuf) {  // keep only the K best so far, then continue scanning
-          warp_select_smallest(bd, bj, td, tj, count, K, lane);
-          count = min(count, K);
-        }
-      }
+      beg = cell_start[row + x0];
+      len = cell_start[row + x1 + 1] - beg;
     }
   }
-  warp_select_smallest(bd, bj, td, tj, count, K, lane);
-  const int kept = min(count, K);
-  for (int e = lane; e < K; e += 32) {
-    const int j = e < kept ? bj[e] : -1;
-    nbr[(size_t)qi * K + e] = j;
-    if (j >= 0) atomicAdd(&indeg[j], 1);
+  int incl = len;
+#pragma unroll
+  for (int o = 1; o < 16; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  const int total = __shfl_sync(0xffffffffu, incl, 8);
+  int rb[9], rx[9];                               // run start in `sorted`, exclusive prefix of the run lengths
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    rb[k] = __shfl_sync(0xffffffffu, beg, k);
+    rx[k] = __shfl_sync(0xffffffffu, incl - len, k);
+  }
+  auto fetch = [&](int f) -> float4 {
+    if (f >= total) return make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+    int sb = rb[0], sx = rx[0];
+#pragma unroll
+    for (int t = 1; t < 9; ++t)
+      if (f >= rx[t]) { sb = rb[t]; sx = rx[t]; }   // the last run whose prefix is <= f (empty runs are passed over)
+    return sorted[sb + (f - sx)];
+  };
+
+  double sel_d[2];
+  int sel_j[2];
+  int count = 0;
+  float4 nxt = fetch(lane);
+  for (int f0 = 0; f0 < total; f0 += 32) {
+    const float4 o = nxt;
+    nxt = fetch(f0 + 32 + lane);
+    const bool valid = f0 + lane < total;
+    const double dx = px - (double)o.x, dyy = py - (double)o.y, dzz = pz - (double)o.z;
+    const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dyy, dyy)), __dmul_rn(dzz, dzz));
+    const bool in = valid && d2 <= r2;
+    const unsigned m = __ballot_sync(0xffffffffu, in);
+    if (in) {
+      const int at = count + __popc(m & ((1u << lane) - 1u));
+      bd[at] = d2;
+      bj[at] = __float_as_int(o.w);
+    }
+    count += __popc(m);
+    __syncwarp();
+    if (count + 32 > kNbrBuf) {  // keep only the K best so far, then continue scanning
+      const int kept = warp_select_smallest(bd, bj, count, K, lane, sel_d, sel_j);
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int e = lane + 32 * i;
+        if (e < kept) { bd[e] = sel_d[i]; bj[e] = sel_j[i]; }
+      }
+      count = kept;
+      __syncwarp();
+    }
+  }
+  const int kept = warp_select_smallest(bd, bj, count, K, lane, sel_d, sel_j);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int e = lane + 32 * i;
+    if (e < K) {
+      const int j = e < kept ? sel_j[i] : -1;
+      nbr[(size_t)qi * K + e] = j;
+      if (j >= 0) atomicAdd(&indeg[j], 1);
+    }
   }
   if (lane == 0) cnt_out[qi] = kept;
 }
@@ -520,7 +564,9 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
   }
   GM_CUDA(launch_pdl(cell_count_kernel, ceil_div(n, T), T, 0, stream, 1, pos, pos_stride, n, n_per_graph, gp, ws.cell_of,
                      ws.cell_cnt));
-  int rc = exclusive_scan_i32(ws.cell_cnt, ws.cell_start, ws.max_cells, ws.scan_ws, stream);
+  // only the cells of the live grid are scanned (device-side bound; the workspace is sized for the worst case)
+  int rc = exclusive_scan_i32(ws.cell_cnt, ws.cell_start, ws.max_cells, ws.scan_ws, stream, nullptr,
+                              &gp->cells_per_graph, n_graphs);
   if (rc) return rc;
   GM_CUDA(launch_pdl(cell_fill_kernel, ceil_div(n, T), T, 0, stream, 1, pos, pos_stride, n, ws.cell_of, ws.cell_start,
                      ws.cell_cnt, ws.sorted));
@@ -533,5 +579,7 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
   return build_recv_csr(nbr, (long long)n * K, nullptr, n, K, edge_ptr, nullptr, ws.indeg, ws.fill, ws.keys,
                         ws.scan_ws, /*indeg_ready=*/true, recv_ptr, esend, erecv, eref, stream, /*fill_ready=*/small);
 }
+
+GM_TRACE_DUMP(trace_dump_radius)
 
 }  // namespace gm

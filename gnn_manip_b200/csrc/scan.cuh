@@ -102,9 +102,13 @@ static __global__ void scan_apply_kernel(const int* __restrict__ in, long long n
 // Small inputs: one block walks the array tile by tile (one launch instead of three).
 constexpr long long kScanSingleBlockMax = 1 << 14;
 static __global__ void scan_single_block_kernel(const int* __restrict__ in, long long n, int* __restrict__ out,
-                                                int* __restrict__ total_out) {
+                                                int* __restrict__ total_out, const int* __restrict__ n_dev,
+                                                int n_mul) {
   pdl_wait();                                 // programmatic dependent launch: see common.cuh
   pdl_launch_dependents();
+  // optional device-side bound: only the first *n_dev * n_mul entries are live (the rest of `in` is zero and the
+  // rest of `out` is never read); out[n_live] receives the total
+  if (n_dev != nullptr) n = min(n, (long long)(*n_dev) * n_mul);
   __shared__ int sm[9];
   int carry = 0;
   for (long long base0 = 0; base0 < n; base0 += kScanTile) {
@@ -142,9 +146,9 @@ static __global__ void scan_copy_total_kernel(const int* __restrict__ out, long 
 // items before writing them and never reads another block's items).
 // total_out (optional, device): receives the grand total as well.
 inline int exclusive_scan_i32(const int* in, int* out, long long n, int* ws, cudaStream_t stream,
-                              int* total_out = nullptr) {
+                              int* total_out = nullptr, const int* n_dev = nullptr, int n_mul = 1) {
   if (n <= kScanSingleBlockMax) {
-    GM_CUDA(launch_pdl(scan_single_block_kernel, 1, kScanThreads, 0, stream, 1, in, n, out, total_out));
+    GM_CUDA(launch_pdl(scan_single_block_kernel, 1, kScanThreads, 0, stream, 1, in, n, out, total_out, n_dev, n_mul));
     GM_LAUNCHED(1);
     GM_LAUNCH_CHECK("scan_single_block_kernel");
     return GM_OK;
