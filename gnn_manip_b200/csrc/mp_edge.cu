@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     };
     // Starts tile k: its layer-1 operand is in TMEM and the staging rows are free.  Segment mask, Pr prefetch,
     // the Ps[send] gather into the staging rows (lands while GEMM 1 runs), operand hand-off, GEMM 1.
-    auto begin_tile = [&](int k) {
+    auto begin_tile = [&](int k, bool issue) {
       cur_recv = nx_recv; cur_send = nx_send; cur_prev = nx_prev;
       const int ge = (blockIdx.x + k * grid) * kTile + r;
       {
@@ -362,8 +362,10 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
 #pragma unroll
       for (int i = 0; i < 4; ++i) prefetch_l1(pr_row + 32 * i);
       stage_rows32_gather(db, b.ps + 4 * lane, cur_send);
-      publish_operand(bar_a, lane);
-      issue_gemm();
+      if (issue) {                               // (inside the loop GEMM 1 was already issued under LayerNorm)
+        publish_operand(bar_a, lane);
+        issue_gemm();
+      }
     };
     if (K0 < n_my) {
       fetch_ids(K0);
@@ -383,7 +385,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
 #ifdef GM_STAMPS
     if (blockIdx.x == 0 && tid == 0) g_edge_stamps[24] = clock64();
 #endif
-    if (K0 < n_my) begin_tile(K0);
+    if (K0 < n_my) begin_tile(K0, true);
     for (int k = K0; k < n_my; k += KSTEP) {
       const int row0 = (blockIdx.x + k * grid) * kTile;
       const int rows_valid = min(kTile, E - row0);
@@ -500,6 +502,12 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
 #pragma unroll
         for (int c = 0; c < 4; ++c) tmem_ld32(tD + c * 32, x + c * 32);
         tmem_ld_wait();
+        // the accumulator is in registers and the next tile's layer-1 operand is in TMEM: its GEMM 1 runs under the
+        // LayerNorm / residual / segmented-sum phases of this tile (E1 of the next tile finds it complete)
+        if (has_next) {
+          publish_operand(bar_a, lane);
+          issue_gemm();
+        }
         GM_ESTAMP(25);
         float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
         // parameters are fetched a whole 32-column box at a time (8 independent 128-bit loads in flight) so that
@@ -639,7 +647,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       GM_ESTAMP(12);
       named_bar_sync(1 + s, kTile);            // every row has been read: the slot's staging tile is free
       GM_ESTAMP(13);
-      if (has_next) begin_tile(k + KSTEP);
+      if (has_next) begin_tile(k + KSTEP, false);
       GM_ESTAMP(14);
     }
   }
