@@ -51,6 +51,7 @@ struct EdgeShared {
   uint64_t d_ready[2];                       // accumulator complete (multicast tcgen05.commit)
   uint32_t tmem_base;
   uint32_t pad;
+  uint64_t a_half[2][2];                     // mp_edge_kernel: K half h of slot s's next operand is in TMEM (4 + 4 arrivals)
   uint32_t segmask[2][4];                    // bit l of word q: row 32q+l starts a new receiver segment
   alignas(16) float prm[4 * kH];             // b2 | b3 | LayerNorm gamma | LayerNorm beta
 };
@@ -229,6 +230,30 @@ __device__ __forceinline__ void publish_operand(uint32_t bar_a_leader, int lane)
   if (lane == 0) mbar_arrive_cluster(bar_a_leader);
 }
 
+// ---- in-place operand layout (mp_edge_kernel): a slot owns two 128-column regions X and Y.  A layer reads its A
+// operand from one and accumulates into the other; the epilogue then overwrites each 32-column block of the
+// accumulator it has just read with the next operand for the same 32 K elements (16 columns bf16 hi + 16 columns
+// lo), so the next layer's MMAs over K elements 0..63 can run while the epilogue still works on columns 64..127. ----
+__device__ __forceinline__ void put_operand32_inplace(const float* v, uint32_t tR, int c32) {
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) split_bf16x2(v[2 * j], v[2 * j + 1], hi[j], lo[j]);
+  tmem_st16(tR + c32 * 32, hi);
+  tmem_st16(tR + c32 * 32 + 16, lo);
+}
+// the 12 MMAs of one K half (64 K elements) of a layer: A (in-place layout) from region tA, weights {Wh.k, Wl.k}
+__device__ __forceinline__ void issue_half_pair(uint32_t w_layer_s, uint32_t tD, uint32_t tA, int half) {
+  const uint32_t wh = w_layer_s + half * kWBlock, wl = w_layer_s + (2 + half) * kWBlock;
+#pragma unroll
+  for (int kk = 0; kk < 4; ++kk) {
+    const int ks = 4 * half + kk;
+    const uint32_t a_hi = tA + 32u * (ks >> 1) + 8u * (ks & 1), a_lo = a_hi + 16u;
+    umma_bf16_ts_pair(tD, a_hi, umma_desc_sw128(wh + kk * 32), kIdescPair, (half | kk) ? 1u : 0u);
+    umma_bf16_ts_pair(tD, a_lo, umma_desc_sw128(wh + kk * 32), kIdescPair, 1u);
+    umma_bf16_ts_pair(tD, a_hi, umma_desc_sw128(wl + kk * 32), kIdescPair, 1u);
+  }
+}
+
 // Phase timestamps (debug aid, -DGM_STAMPS): thread 0 of CTA 0 (slot 0) records clock64() during its third tile,
 // the MMA issuer during the matching pair; read back with gm_debug_stamps() (entries 0..31).
 #ifdef GM_STAMPS
@@ -261,7 +286,8 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
   if (tid == 0) {
     mbar_init(smem_u32(&sh->w_full), 1);
     for (int s = 0; s < 2; ++s) {
-      mbar_init(smem_u32(&sh->a_ready[s]), 8);
+      mbar_init(smem_u32(&sh->a_half[s][0]), 8);
+      mbar_init(smem_u32(&sh->a_half[s][1]), 8);
       mbar_init(smem_u32(&sh->d_ready[s]), 1);
     }
     fence_mbar_init();
@@ -301,25 +327,65 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     uint32_t ro[8];                            // row-owner offsets of the 8 chunks of a box
 #pragma unroll
     for (int j = 0; j < 8; ++j) ro[j] = stage_chunk_off(r, j);
-    const uint32_t tD = tmem + ((uint32_t)r0 << 16) + 256u * s, tAH = tD + 128u, tAL = tD + 192u;
-    const uint32_t bar_a_local = smem_u32(&sh->a_ready[s]), bar_d = smem_u32(&sh->d_ready[s]);
-    const uint32_t bar_a = mapa_shared(bar_a_local, 0);   // the leader CTA's barrier, cluster address space
+    // regions of this slot: layer 1 reads X and accumulates into Y, layer 2 reads Y -> X, layer 3 reads X -> Y
+    const uint32_t tXs = tmem + 256u * s, tYs = tXs + 128u;                      // MMA addresses (lane 0)
+    const uint32_t tX = tXs + ((uint32_t)r0 << 16), tY = tYs + ((uint32_t)r0 << 16);   // this warp's lanes
+    const uint32_t bar_a0_local = smem_u32(&sh->a_half[s][0]), bar_a1_local = smem_u32(&sh->a_half[s][1]);
+    const uint32_t bar_d = smem_u32(&sh->d_ready[s]);
+    const uint32_t bar_a0 = mapa_shared(bar_a0_local, 0), bar_a1 = mapa_shared(bar_a1_local, 0);   // leader CTA's
     const bool issuer = rank == 0 && q == 0 && lane == 0;
     const float* prm = sh->prm;
     uint32_t ph_d = 0, ph_a = 0;
     int layer = 0;
     // leader, one thread per slot: once both CTAs have published the operand, issue the layer's 24 MMAs for the
     // pair and commit to d_ready in both CTAs.  The two slots' issuers interleave on the tensor pipe in readiness order.
+    bool issued0 = false;
+    auto issue_half = [&](int half) {
+      const uint32_t tA = layer == 1 ? tYs : tXs, tDst = layer == 1 ? tXs : tYs;
+      issue_half_pair(W_s + layer * kWLayer, tDst, tA, half);
+    };
+    // this warp's part of K half h of the next operand is in TMEM
+    auto publish_half = [&](int half) {
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(half ? bar_a1 : bar_a0);
+    };
+    // issuer only, non-blocking: start the next layer on K half 0 as soon as every warp of the pair has published it
+    auto poll_half0 = [&]() {
+      if (issuer && !issued0 && mbar_try_wait(bar_a0_local, ph_a)) {
+        tc_fence_after();
+        issue_half(0);
+        issued0 = true;
+      }
+      __syncwarp();
+    };
+    // after this warp published half 1: the issuer completes the layer's MMAs and commits to d_ready in both CTAs
     auto issue_gemm = [&]() {
       if (issuer) {
-        mbar_wait(bar_a_local, ph_a);
+        if (!issued0) {
+          mbar_wait(bar_a0_local, ph_a);
+          tc_fence_after();
+          issue_half(0);
+        }
+        mbar_wait(bar_a1_local, ph_a);
         tc_fence_after();
-        issue_layer_pair(W_s + layer * kWLayer, tmem + 256u * s, tmem + 256u * s + 128u, tmem + 256u * s + 192u);
+        issue_half(1);
         umma_commit_pair(bar_d);
       }
+      issued0 = false;
       ph_a ^= 1u;
       layer = layer == 2 ? 0 : layer + 1;
       __syncwarp();
+    };
+    auto publish_both = [&]() {
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive_cluster(bar_a0);
+        mbar_arrive_cluster(bar_a1);
+      }
     };
 
     int nx_recv = -1, nx_send = -1, nx_prev = -2;
@@ -345,7 +411,16 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     auto operand_from_stage = [&]() {
       cp_async_wait_all();
       __syncwarp();
-      row_to_operand(S, ro, tAH, tAL);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 t = *reinterpret_cast<const float4*>(S + c * kBoxBytes + ro[j]);
+          v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+        }
+        put_operand32_inplace(v, tX, c);
+      }
       tmem_st_wait();
       __syncwarp();                            // every lane is done reading this warp's rows
     };
@@ -363,7 +438,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       for (int i = 0; i < 4; ++i) prefetch_l1(pr_row + 32 * i);
       stage_rows32_gather(db, b.ps + 4 * lane, cur_send);
       if (issue) {                               // (inside the loop GEMM 1 was already issued under LayerNorm)
-        publish_operand(bar_a, lane);
+        publish_both();
         issue_gemm();
       }
     };
@@ -421,31 +496,33 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
             v[4 * j + 2] = fmaxf(v[4 * j + 2] + (p[j].z + s4.z), 0.f);
             v[4 * j + 3] = fmaxf(v[4 * j + 3] + (p[j].w + s4.w), 0.f);
           }
-          put_operand32(v, tAH, tAL, c);
+          put_operand32_inplace(v, tY, c);
         };
-        tmem_ld32(tD, va);
+        tmem_ld32(tY, va);
         load_pr(0, pa);
         load_pr(1, pb);
         tmem_ld_wait();
         GM_ESTAMP(16);
-        tmem_ld32(tD + 32, vb);
+        tmem_ld32(tY + 32, vb);
         e1_block(0, va, pa);
         GM_ESTAMP(17);
         load_pr(2, pa);
         tmem_ld_wait();
-        tmem_ld32(tD + 64, va);
+        tmem_ld32(tY + 64, va);
         e1_block(1, vb, pb);
+        publish_half(0);                           // K elements 0..63 of the layer-2 operand
         GM_ESTAMP(18);
         load_pr(3, pb);
         tmem_ld_wait();
-        tmem_ld32(tD + 96, vb);
+        tmem_ld32(tY + 96, vb);
         e1_block(2, va, pa);
+        poll_half0();
         GM_ESTAMP(19);
         tmem_ld_wait();
         e1_block(3, vb, pb);
         GM_ESTAMP(20);
       }
-      publish_operand(bar_a, lane);
+      publish_half(1);
       GM_ESTAMP(21);
       issue_gemm();
       GM_ESTAMP(22);
@@ -471,22 +548,24 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
             v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs[j].z, 0.f);
             v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs[j].w, 0.f);
           }
-          put_operand32(v, tAH, tAL, c);
+          put_operand32_inplace(v, tX, c);
         };
-        tmem_ld32(tD, va);
+        tmem_ld32(tX, va);
         tmem_ld_wait();
-        tmem_ld32(tD + 32, vb);
+        tmem_ld32(tX + 32, vb);
         e2_block(0, va);
         tmem_ld_wait();
-        tmem_ld32(tD + 64, va);
+        tmem_ld32(tX + 64, va);
         e2_block(1, vb);
+        publish_half(0);
         tmem_ld_wait();
-        tmem_ld32(tD + 96, vb);
+        tmem_ld32(tX + 96, vb);
         e2_block(2, va);
+        poll_half0();
         tmem_ld_wait();
         e2_block(3, vb);
       }
-      publish_operand(bar_a, lane);
+      publish_half(1);
       issue_gemm();
       GM_ESTAMP(8);
       // ---- layer 3 epilogue: y = LayerNorm(D + b3) -> staging row ----
@@ -500,12 +579,12 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
         // the whole accumulator row lives in registers: exact two-pass LayerNorm, thread-local
         float x[kH];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) tmem_ld32(tD + c * 32, x + c * 32);
+        for (int c = 0; c < 4; ++c) tmem_ld32(tY + c * 32, x + c * 32);
         tmem_ld_wait();
         // the accumulator is in registers and the next tile's layer-1 operand is in TMEM: its GEMM 1 runs under the
         // LayerNorm / residual / segmented-sum phases of this tile (E1 of the next tile finds it complete)
         if (has_next) {
-          publish_operand(bar_a, lane);
+          publish_both();
           issue_gemm();
         }
         GM_ESTAMP(25);
