@@ -524,11 +524,11 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
       }
       publish_half(1);
       GM_ESTAMP(21);
+      // the staging rows are free until the LayerNorm rows go in: the e rows of this slot's next tile land here
+      // while layers 2 and 3 run (issued before the issuer blocks on the other warps' hand-off)
+      if (has_next) stage_e_rows(k + KSTEP);
       issue_gemm();
       GM_ESTAMP(22);
-      // the staging rows are free until the LayerNorm rows go in: the e rows of this slot's next tile land here
-      // while layers 2 and 3 run
-      if (has_next) stage_e_rows(k + KSTEP);
       GM_ESTAMP(6);
       // ---- layer 2 epilogue: relu(D + b2) ----
       mbar_wait(bar_d, ph_d);
@@ -583,10 +583,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
         tmem_ld_wait();
         // the accumulator is in registers and the next tile's layer-1 operand is in TMEM: its GEMM 1 runs under the
         // LayerNorm / residual / segmented-sum phases of this tile (E1 of the next tile finds it complete)
-        if (has_next) {
-          publish_both();
-          issue_gemm();
-        }
+        if (has_next) publish_both();              // (the issuer picks it up after its own LayerNorm, below)
         GM_ESTAMP(25);
         float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
         // parameters are fetched a whole 32-column box at a time (8 independent 128-bit loads in flight) so that
@@ -632,6 +629,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
         }
       }
       __syncwarp();
+      if (has_next) issue_gemm();                  // by now every warp of the pair has published: no stall for the issuer
       GM_ESTAMP(10);
       // ---- e' = e + y (epd_gnn.py:104): this warp's rows leave as 512 B vector reductions, the add happens in L2 ----
       {
