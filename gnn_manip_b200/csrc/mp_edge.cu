@@ -815,16 +815,8 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
     if (ge < E) return edge_feature(pos, pos_stride, __ldg(g.esend + ge), __ldg(g.erecv + ge), conn_r);
     return make_float4(0.f, 0.f, 0.f, 0.f);
   };
-  float4 xn = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (s < n_my) xn = load_x(s);
-  mbar_wait(smem_u32(&sh->w_full), 0);
-  cluster_sync_all();
-  for (int k = s; k < n_my; k += 2) {
-    const int row0 = (blockIdx.x + k * grid) * kTile;
-    const int rows_valid = min(kTile, E - row0);
-    const float4 x = xn;
-    if (k + 2 < n_my) xn = load_x(k + 2);          // in flight during this tile
-    // ---- layer 1 on CUDA cores: relu(W1 x + b1) -> bf16 hi / lo operand in TMEM (same FMA order as the SIMT path) ----
+  // layer 1 on CUDA cores: relu(W1 x + b1) -> bf16 hi / lo operand in TMEM (same FMA order as the SIMT path)
+  auto layer1 = [&](const float4& x) {
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       float v[32];
@@ -835,8 +827,23 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
       }
       put_operand32(v, tAH, tAL, c);
     }
+  };
+  float4 xn = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (s < n_my) xn = load_x(s);
+  mbar_wait(smem_u32(&sh->w_full), 0);
+  cluster_sync_all();
+  if (s < n_my) {                                  // first tile of the slot: operand and GEMM 2 up front
+    layer1(xn);
     publish_operand(bar_a, lane);
     issue_gemm();
+    if (s + 2 < n_my) xn = load_x(s + 2);
+  }
+  for (int k = s; k < n_my; k += 2) {
+    const int row0 = (blockIdx.x + k * grid) * kTile;
+    const int rows_valid = min(kTile, E - row0);
+    const bool has_next = k + 2 < n_my;
+    const float4 x_next = xn;                      // features of this slot's next tile (loaded during the previous one)
+    if (k + 4 < n_my) xn = load_x(k + 4);          // in flight during this tile
     // ---- layer 2 epilogue: relu(D + b2) ----
     mbar_wait(bar_d, ph_d);
     ph_d ^= 1u;
@@ -873,11 +880,15 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
     mbar_wait(bar_d, ph_d);
     ph_d ^= 1u;
     tc_fence_after();
+    // the operand region is free (GEMM 3 is complete): the next tile's layer 1 goes in now, and its GEMM 2 runs
+    // under this tile's LayerNorm and row stores once every warp has the accumulator in registers
+    if (has_next) layer1(x_next);
     {
       float y[kH];
 #pragma unroll
       for (int c = 0; c < 4; ++c) tmem_ld32(tD + c * 32, y + c * 32);
       tmem_ld_wait();
+      if (has_next) publish_operand(bar_a, lane);
       float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
 #pragma unroll
       for (int j = 0; j < kH / 4; ++j) {
@@ -904,6 +915,7 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
       }
     }
     __syncwarp();
+    if (has_next) issue_gemm();                    // every warp of the pair has published by now
     // ---- this warp's 32 rows leave as coalesced 512 B stores ----
     {
       const int nr = min(32, rows_valid - r0);
