@@ -157,6 +157,11 @@ __device__ unsigned long long g_stamps[64];
 #else
 #define GM_STAMP(i) do { } while (0)
 #endif
+#ifdef GM_STAMPS
+#define GM_NF(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_stamps[i] = clock64(); } while (0)
+#else
+#define GM_NF(i) do { } while (0)
+#endif
 
 // byte offset of logical (row, col8-group) inside a SWIZZLE_128B K-major bf16 image
 __device__ __forceinline__ uint32_t a_off(int row, int col) {
@@ -440,7 +445,9 @@ __device__ __forceinline__ void node_finish(Ctx& c, char* A0, char* T, const flo
                                             const TcBuffers& b, int node0, int rows_valid) {
   {
     float x[64];
+    GM_NF(44);
     ln_row64(c, prm, x);
+    GM_NF(45);
     const bool live = c.row < rows_valid;
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
@@ -455,21 +462,30 @@ __device__ __forceinline__ void node_finish(Ctx& c, char* A0, char* T, const flo
 #pragma unroll
     for (int gq = 0; gq < 8; ++gq) store_a8(A0, c.row, c.hf * 64 + 8 * gq, x + 8 * gq);
   }
+  GM_NF(46);
   launch_gemm(c, 0, 1, false);                         // v' Wr^T   |   decoder layer 1
+  GM_NF(47);
   copy_out_rows(c, T, b.v, node0, rows_valid);         // overlaps the GEMM
+  GM_NF(48);
   wait_gemm(c, 0);
+  GM_NF(49);
   if (!has_dec) {
     load_w(c, next.wc[4]);
     __syncthreads();                                   // every warp is done reading v' out of T
     d_to_stage(c, T, next.b1);                         // Pr carries b1 of the next edge MLP (mp_edge.cu adds no bias)
+    GM_NF(50);
     launch_gemm(c, 0, 1, false);                       // v' Ws^T
+    GM_NF(51);
     copy_out_rows(c, T, b.pr, node0, rows_valid);
     wait_gemm(c, 0);
+    GM_NF(52);
     __syncthreads();
     d_to_stage(c, T);
     tc_fence_before();
     __syncthreads();
+    GM_NF(53);
     copy_out_rows(c, T, b.ps, node0, rows_valid);
+    GM_NF(54);
   } else {
     // decoder: Linear+ReLU, Linear+ReLU on the tensor cores, Linear(128 -> out_dim) on CUDA cores (epd_gnn.py:49,96)
     load_w(c, next.wc[1]);

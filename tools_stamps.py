@@ -19,3 +19,4 @@ print("edge E1 fine stamps (since stamp 5: ld0 done, blk0, blk1, blk2, blk3, pub
 print("edge LN fine stamps (since stamp 2: acc loaded, mean, rstd; stamp 10 = rows stored):", [int(x - s[2]) for x in (s[25], s[26], s[27], s[10])])
 print("edge pdl wait (cycles):", int(s[24] - s[23]))
 print("node stamps:", [int(x - s[32]) for x in s[32:44]])
+print("node_finish stamps (since 44: ln, a0, launch Wr, copy v, wait, stage Pr, launch Ws, wait, stage Ps, copy Ps):", [int(x - s[44]) for x in s[45:55]])
