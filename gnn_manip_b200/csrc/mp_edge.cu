@@ -449,7 +449,11 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     // weights of this CTA landed; peer barriers initialised, peer weights landed, TMEM of the pair allocated
     mbar_wait(smem_u32(&sh->w_full), 0);
     cluster_sync_all();
-    if (K0 < n_my) operand_from_stage();
+    if (K0 < n_my) {
+      operand_from_stage();
+      publish_both();                            // layer 1 of the first tile needs e and weights only: its GEMM runs
+      issue_gemm();                              // before the dependency wait as well
+    }
     // Everything so far read only constants and e, which the kernel two launches back (the previous edge kernel /
     // the edge encoder) finished writing before this grid could start; Pr / Ps come from the node kernel right before.
 #ifdef GM_STAMPS
@@ -460,7 +464,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
 #ifdef GM_STAMPS
     if (blockIdx.x == 0 && tid == 0) g_edge_stamps[24] = clock64();
 #endif
-    if (K0 < n_my) begin_tile(K0, true);
+    if (K0 < n_my) begin_tile(K0, false);
     for (int k = K0; k < n_my; k += KSTEP) {
       const int row0 = (blockIdx.x + k * grid) * kTile;
       const int rows_valid = min(kTile, E - row0);
