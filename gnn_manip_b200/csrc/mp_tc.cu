@@ -564,6 +564,8 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
     // layer 1, node part first: D = v W1b^T needs nothing from this step's edge kernel, so for the first tile it runs
     // (weights, operand and MMAs) while that kernel is still draining; the aggregated-edge part accumulates on top
     launch_gemm(c, 1, 1, false);                   // sub 0 of launch_gemm(c, 1, ...) reads A buffer 1 (= T), TMEM cols 0
+    // receiver CSR offsets of this warp's rows (graph data, older than the edge kernel): fetched before the wait too
+    const int rp = __ldg(g.recv_ptr + min(node0 + c.warp * R + min(c.lane, R), g.n_nodes));
     wait_gemm(c, 0);
     load_w(c, m.wc[0]);
     if (tile == (int)blockIdx.x) {
@@ -573,8 +575,6 @@ mp_node_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restrict_
     // ---- prologue: total aggregate per node (first-tile partial + carries of the following agg tiles) -> A0,
     //      node latents -> T (as the second layer-1 operand) ----
     {
-      const int nl = min(node0 + c.warp * R + min(c.lane, R), g.n_nodes);
-      const int rp = __ldg(g.recv_ptr + nl);
       float4 x[R];
       int sb[R], se[R];
 #pragma unroll

@@ -112,8 +112,8 @@ __global__ void integrate_kernel(float* __restrict__ obs, const float* __restric
   pdl_launch_dependents();
   const int node = blockIdx.x * blockDim.x + threadIdx.x;
   const int n = rp.n_graphs * rp.n_per_graph;
-  if (node >= n) return;
   const int k = rp.k, D = rp.D;
+  if (node < n) {
   const PhysParams& p = rp.phys;
   float nxt[3];
   {
@@ -153,12 +153,17 @@ __global__ void integrate_kernel(float* __restrict__ obs, const float* __restric
 #pragma unroll
     for (int d = 0; d < 3; ++d) last[p.cart[d]] = nxt[d];
   }
-}
-
-__global__ void bump_step_kernel(int* step_dev) {
-  pdl_wait();                                 // programmatic dependent launch: see common.cuh
-  pdl_launch_dependents();
-  if (threadIdx.x == 0 && blockIdx.x == 0) *step_dev += 1;
+  }
+  // step counter: the last block to get here advances it (every block has read it by then); step_dev[1] is the ticket
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int t = atomicAdd(rp.step_dev + 1, 1);
+    if (t == (int)gridDim.x - 1) {
+      rp.step_dev[1] = 0;
+      rp.step_dev[0] += 1;
+    }
+  }
 }
 
 }  // namespace
@@ -194,8 +199,7 @@ int apply_control(float* obs, const RolloutParams& rp, cudaStream_t stream) {
 int integrate(float* obs, const float* pred, const RolloutParams& rp, float* next_pos_out, cudaStream_t stream) {
   const int n = rp.n_graphs * rp.n_per_graph;
   GM_CUDA(launch_pdl(integrate_kernel, ceil_div(n, 128), 128, 0, stream, 1, obs, pred, rp, next_pos_out));
-  GM_CUDA(launch_pdl(bump_step_kernel, 1, 32, 0, stream, 1, rp.step_dev));
-  GM_LAUNCHED(2);
+  GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("integrate_kernel");
   return GM_OK;
 }
