@@ -191,7 +191,10 @@ typedef struct gm_rollout_desc {
 size_t gm_rollout_workspace_bytes(const gm_rollout_desc* desc_host);
 int gm_rollout_create(gm_rollout** plan, const gm_rollout_desc* desc_host, void* workspace, size_t workspace_bytes,
                       void* stream);
-/* run `steps` rollout steps starting at the plan's current step index (reset with gm_rollout_reset). */
+/* run `steps` rollout steps starting at the plan's current step index (reset with gm_rollout_reset).  A tensor-core
+ * plan owns one extra CUDA stream and two events (no device memory): the node encoder of each step is forked onto
+ * it beside the graph build and joined back into `stream` before the first message-passing step, so all work is
+ * still ordered by `stream` from the caller's point of view. */
 int gm_rollout_run(gm_rollout* plan, int32_t steps, void* stream);
 int gm_rollout_reset(gm_rollout* plan, int32_t step, void* stream);
 /* device pointers into the plan's workspace holding the graph of the most recent step (for parity tests) */
