@@ -9,12 +9,14 @@ ng = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 torch.manual_seed(0)
 model = gm.EncProcDecGNN(25, 4, 3, 128, 2, 10)
 obs, _ = scenes.make_state(n, seed=0, n_rigid=min(scenes.N_RIGID, n // 2))
-rot, ty = bench.control_curve(20, 0)
+curves = [bench.control_curve(20, i) for i in range(ng)]
+rot = np.stack([c[0] for c in curves]) if ng > 1 else curves[0][0]
+ty = np.stack([c[1] for c in curves]) if ng > 1 else curves[0][1]
 plan = gm.Rollout(model, bench.make_graph_attr(gm), obs, rot=rot, ty=ty, ty_init=tuple(scenes.TY_INIT),
-                  use_cuda_graph=True, impl=gm._lib.GM_IMPL_TC)
+                  n_graphs=ng, use_cuda_graph=True, impl=gm._lib.GM_IMPL_TC)
 buf = (ctypes.c_ulonglong * (4 * 161))()
 dump = lambda: gm._lib.check(gm._lib.lib().gm_debug_stamps(buf, 4 * 161), "gm_debug_stamps")
-plan.run(5); torch.cuda.synchronize(); dump()
+plan.run(12); torch.cuda.synchronize(); dump()
 plan.run(2); torch.cuda.synchronize(); dump()
 s = np.array(buf[:], dtype=np.int64)
 names = ["physics", "radius", "node", "edge"]
