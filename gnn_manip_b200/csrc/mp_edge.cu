@@ -35,7 +35,8 @@ namespace gm {
 
 namespace {
 
-constexpr int kNTE = 256;                    // two compute warpgroups; one elected thread per slot issues the MMAs
+constexpr int kNTE = 256;                    // enc_edge: two compute warpgroups; one elected thread per slot issues the MMAs
+constexpr int kNTE3 = 384;                   // mp_edge: two compute warpgroups + the MMA-issuer warpgroup
 constexpr int kPieceBytes = 16384;           // one K block (64 columns) of one 128-row bf16 image (self test)
 constexpr int kWBlock = 8192;                // this CTA's 64 weight rows of one K block of one image
 constexpr int kWLayer = 4 * kWBlock;         // {Wh.k0, Wh.k1, Wl.k0, Wl.k1}
@@ -271,7 +272,7 @@ constexpr int kOffB2 = 0, kOffB3 = 128, kOffG = 256, kOffBeta = 384;
 
 }  // namespace
 
-__global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, TcBuffers b) {
+__global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, TcBuffers b) {
   extern __shared__ __align__(1024) char smem_raw[];
   char* base = smem_raw;
   const uint32_t W_s = smem_u32(base);
@@ -299,7 +300,7 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
                  kWBlock, smem_u32(&sh->w_full));
   }
   if (warp == 0) tmem_alloc_pair(smem_u32(&sh->tmem_base), 512);
-  for (int i = tid; i < kH; i += kNTE) {
+  for (int i = tid; i < kH; i += kNTE3) {
     sh->prm[kOffB2 + i] = m.b2[i];
     sh->prm[kOffB3 + i] = m.b3[i];
     sh->prm[kOffG + i] = m.ln_g[i];
@@ -318,7 +319,43 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
   // iteration still takes part in every hand-off with zero valid rows
   const int b_lead = (int)blockIdx.x - (int)rank;
   const int n_my = b_lead < n_tiles ? (n_tiles - b_lead + grid - 1) / grid : 0;
-  {
+  if (warp >= 8) {
+    // ---------------- third warpgroup: gives its registers to the compute warpgroups; its first lane in the
+    //                  leader CTA issues every MMA of both slots (nothing else ever blocks on the tensor pipe) ----
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    mbar_wait(smem_u32(&sh->w_full), 0);
+    cluster_sync_all();                        // pairs with the compute warpgroups' prologue barrier
+    if (warp == 8 && lane == 0 && rank == 0) {
+      // items of a slot, in order: (tile, layer, K half); a_half[s][h] is used once per layer -> parity (item / 2) & 1
+      int it[2] = {0, 0};
+      const int end[2] = {6 * ((n_my + 1) / 2), 6 * (n_my / 2)};
+      uint32_t idle = 0;
+      while (it[0] < end[0] || it[1] < end[1]) {
+        bool progress = false;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          if (it[s] < end[s]) {
+            const int half = it[s] & 1, layer = (it[s] >> 1) % 3;
+            if (mbar_try_wait(smem_u32(&sh->a_half[s][half]), (uint32_t)(it[s] >> 1) & 1u)) {
+              tc_fence_after();
+              const uint32_t tXs = tmem + 256u * s, tYs = tXs + 128u;
+              issue_half_pair(W_s + layer * kWLayer, layer == 1 ? tXs : tYs, layer == 1 ? tYs : tXs, half);
+              if (half) umma_commit_pair(smem_u32(&sh->d_ready[s]));
+              ++it[s];
+              progress = true;
+            }
+          }
+        }
+        if (progress) idle = 0;
+        else if (++idle > (1u << 28)) {
+          printf("gnn_manip_b200: mp_edge issuer timed out (block %d)\n", blockIdx.x);
+          __trap();
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     // ---------------- compute warpgroups: slot s, thread = edge row r ----------------
     const int s = warp >> 2, q = warp & 3, r = tid & (kTile - 1), r0 = q * 32;
     const int KSTEP = 2, K0 = s;             // slot s takes this CTA's tiles s, s + 2, ...
@@ -333,51 +370,19 @@ __global__ void __launch_bounds__(kNTE, 1) mp_edge_kernel(TcMlp m, TcGraph g, Tc
     const uint32_t bar_a0_local = smem_u32(&sh->a_half[s][0]), bar_a1_local = smem_u32(&sh->a_half[s][1]);
     const uint32_t bar_d = smem_u32(&sh->d_ready[s]);
     const uint32_t bar_a0 = mapa_shared(bar_a0_local, 0), bar_a1 = mapa_shared(bar_a1_local, 0);   // leader CTA's
-    const bool issuer = rank == 0 && q == 0 && lane == 0;
     const float* prm = sh->prm;
-    uint32_t ph_d = 0, ph_a = 0;
-    int layer = 0;
+    uint32_t ph_d = 0;
     // leader, one thread per slot: once both CTAs have published the operand, issue the layer's 24 MMAs for the
     // pair and commit to d_ready in both CTAs.  The two slots' issuers interleave on the tensor pipe in readiness order.
-    bool issued0 = false;
-    auto issue_half = [&](int half) {
-      const uint32_t tA = layer == 1 ? tYs : tXs, tDst = layer == 1 ? tXs : tYs;
-      issue_half_pair(W_s + layer * kWLayer, tDst, tA, half);
-    };
-    // this warp's part of K half h of the next operand is in TMEM
+    // this warp's part of K half h of the next operand is in TMEM (the issuer warp takes it from there)
     auto publish_half = [&](int half) {
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(half ? bar_a1 : bar_a0);
     };
-    // issuer only, non-blocking: start the next layer on K half 0 as soon as every warp of the pair has published it
-    auto poll_half0 = [&]() {
-      if (issuer && !issued0 && mbar_try_wait(bar_a0_local, ph_a)) {
-        tc_fence_after();
-        issue_half(0);
-        issued0 = true;
-      }
-      __syncwarp();
-    };
-    // after this warp published half 1: the issuer completes the layer's MMAs and commits to d_ready in both CTAs
-    auto issue_gemm = [&]() {
-      if (issuer) {
-        if (!issued0) {
-          mbar_wait(bar_a0_local, ph_a);
-          tc_fence_after();
-          issue_half(0);
-        }
-        mbar_wait(bar_a1_local, ph_a);
-        tc_fence_after();
-        issue_half(1);
-        umma_commit_pair(bar_d);
-      }
-      issued0 = false;
-      ph_a ^= 1u;
-      layer = layer == 2 ? 0 : layer + 1;
-      __syncwarp();
-    };
+    auto poll_half0 = [&]() {};
+    auto issue_gemm = [&]() {};
     auto publish_both = [&]() {
       tmem_st_wait();
       tc_fence_before();
@@ -1047,7 +1052,7 @@ int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_
   const int grid = min((ceil_div(g.max_edges, kTile) + 1) & ~1, kNumSMs & ~1);
   // programmatic = false: fully ordered after everything before it in the stream (its early part reads e, which
   // must then come from the kernel right before it or from a joined stream)
-  GM_CUDA(launch_ex(mp_edge_kernel, grid, kNTE, (size_t)kEdgeSmemBytes, stream, 2, programmatic, m, g, b));
+  GM_CUDA(launch_ex(mp_edge_kernel, grid, kNTE3, (size_t)kEdgeSmemBytes, stream, 2, programmatic, m, g, b));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("mp_edge_kernel");
   return GM_OK;
