@@ -3,22 +3,25 @@
 // Replaces EdgeModel.forward (deps/torch-graphnet/torch_graphnet/graph_networks.py:29-50), the residual of
 // EncProcDecGNN._process (gnn_manip/models/epd_gnn.py:104) and scatter_sum (utils/gn_utils.py:60-64).
 //
-// Persistent CTA pairs (clusters of 2, one CTA per SM), 256 threads per CTA:
-//   warps 0-3  compute warpgroup of tile slot 0   } thread = one edge row of a 128-edge tile: operand split,
-//   warps 4-7  compute warpgroup of tile slot 1   } bias/ReLU/LayerNorm epilogues, segmented receiver sum
+// Persistent CTA pairs (clusters of 2, one CTA per SM).  mp_edge_kernel: 384 threads per CTA
+//   warps 0-3   compute warpgroup of tile slot 0   } thread = one edge row of a 128-edge tile: operand split,
+//   warps 4-7   compute warpgroup of tile slot 1   } bias/ReLU/LayerNorm epilogues, segmented receiver sum
+//   warps 8-11  hand their registers to the compute warpgroups (setmaxnreg 40 / 232); lane 0 of warp 8 in the
+//               leader CTA issues every MMA of both slots, so no compute warp ever blocks on the tensor pipe
+// (enc_edge_pair_kernel: 256 threads, lane 0 of each slot's first warp issues.)
 // Each CTA has two 128-edge tiles in flight (one per warpgroup).  A layer of a slot runs as ONE M = 256 GEMM over
 // the pair (tcgen05.mma.cta_group::2): 128 rows of A from each CTA's tensor memory, the weight rows split 64 + 64
 // between the two CTAs' shared memories.  Halving the weights per CTA is what lets all three layers (bf16 hi + lo,
 // 96 KB per CTA) stay resident for the whole kernel: no weight streaming, no weight traffic in L2 after the prologue.
-// The leader CTA's lane 0 of each slot's first warp issues the slot's MMAs once both CTAs have published the
-// operand (remote mbarrier arrive), and commits to the d_ready barrier of both CTAs (multicast); the two slots'
-// GEMMs interleave on the tensor pipe in readiness order while the other slot's warps run their epilogue.
+// The issuer waits for each K half of an operand (remote mbarrier arrives from both CTAs), issues its 12 MMAs and
+// commits a finished layer to the d_ready barrier of both CTAs (multicast); the two slots' GEMMs interleave on the
+// tensor pipe in readiness order while the other slot's warps run their epilogue.
 //
 // Memory plan
-//   TMEM (512 columns): per slot 128 fp32 accumulator columns + the A operand of the next GEMM as bf16 hi / lo
-//     images (64 + 64 columns, lane = edge row, two K elements per 32-bit column).  Epilogues write the next A
-//     operand straight into TMEM with tcgen05.st -- no swizzled shared-memory operand, no st.shared bandwidth --
-//     and the MMAs read A from TMEM and only the weights from shared memory.
+//   TMEM (512 columns): per slot two 128-column regions; a layer reads its A operand (bf16 hi / lo, lane = edge
+//     row, two K elements per 32-bit column) from one and accumulates fp32 into the other.  Epilogues write the
+//     next A operand with tcgen05.st in place over the accumulator block they have just read -- no swizzled
+//     shared-memory operand, no st.shared bandwidth -- and the MMAs read A from TMEM and only weights from smem.
 //   SMEM: 96 KB of weights; one 64 KB fp32 staging tile per slot, stored as four 32-column boxes of 128 x 128 B
 //     with the 16-byte chunk index XOR (row & 7): conflict-free for row-owner 128-bit access and for column-owner
 //     32-bit access.  Each warp stages exactly the 32 rows its own threads own (cp.async, one coalesced 512 B row
