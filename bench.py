@@ -351,6 +351,14 @@ def run_ours(args):
         line["roofline"] = roofline_entry(per[2], E, pk, sustained=True)
         line["roofline"]["note"] = ("C2 graph (L2-resident latents, launch/latency-bound regime); "
                                     "see roofline_c3 for the 100k-particle cloud")
+        try:   # DRAM bytes of the same launch from the committed ncu capture (never measured under this run)
+            with open(os.path.join(ROOT, "profiles", "mp_edge_traffic.json")) as f:
+                tr = json.load(f)["c2"]
+            if int(tr["edges_per_launch"]) == int(E):
+                line["roofline"]["traffic"] = tr["dram_bytes_per_launch"]
+                line["roofline"]["traffic_source"] = tr["source"]
+        except (OSError, KeyError, ValueError):
+            pass
         line["kernel_us_c2"] = {"enc_edge": 1e3 * per[0], "enc_node": 1e3 * per[1], "mp_edge": 1e3 * per[2],
                                 "mp_node": 1e3 * per[3]}
         if not args.no_c3:
