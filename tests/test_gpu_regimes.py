@@ -1,0 +1,225 @@
+"""GPU parity suite, part 2 (-m gpu): the tensor-core path (impl=2) in the regimes bench.py measures.
+
+Round-1 parity stopped at about 300 edge tiles (two tiles per tile slot).  These cases run the steady-state loops of
+mp_edge / mp_node / enc_edge tens of iterations deep (C3: 100 000 particles, about 2 M edges; C4: 64 candidates
+batched as disjoint graphs, 2.56 M edges), the carry path of the segmented sum across many 64-row blocks, batched
+graphs on the tcgen05 path, the post-trajectory branch of the rollout and the 300-step horizon of BASELINE.json
+configs[1].  Everything goes through the C ABI.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, rel_l2
+from oracle import scene
+from test_gpu_parity import ACC_TOL_SIMT, ACC_TOL_TC, make_graph_attr, oracle_features, seeded_models
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gm():
+    import gnn_manip_b200
+    assert torch.cuda.is_available(), "the gpu suite needs a CUDA device"
+    return gnn_manip_b200
+
+
+def device_forward(gm, model, obs, impl, n_graphs=1):
+    """Forward on the device-built graph of `obs` (on-the-fly edge features, the rollout's code path)."""
+    import ctypes  # noqa: F401
+    L, lib = gm._lib.lib(), gm._lib
+    dev = torch.device("cuda", torch.cuda.current_device())
+    o = obs.to(dev)
+    nodes = make_graph_attr(gm).compute_nodes(o)
+    pos = o[-1][:, scene.CART_IDX].contiguous()
+    g = gm.radius_graph(pos, scene.CONN_R, scene.MAX_NBRS, n_graphs=n_graphs)
+    E, N = g.n_edges, pos.shape[0]
+    pm = model.packed(dev)
+    pred = torch.empty((N, 3), device=dev)
+    ws_bytes = L.gm_forward_workspace_bytes(pm.handle, N, E, impl)
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+    lib.check(L.gm_model_forward(pm.handle, impl, lib.ptr(nodes), None, lib.ptr(pos), 3, scene.CONN_R, N, E,
+                                 lib.ptr(g.n_edges_dev), lib.ptr(g.recv_ptr), lib.ptr(g.esend), lib.ptr(g.erecv),
+                                 lib.ptr(g.eref), lib.ptr(pred), lib.ptr(ws), ws_bytes, lib.stream_ptr(dev)),
+              "gm_model_forward")
+    torch.cuda.synchronize()
+    return pred.cpu(), E
+
+
+# ---------------------------------------------------------------------------------------------------------
+# model forward, many tiles per tile slot
+# ---------------------------------------------------------------------------------------------------------
+def test_forward_20k_matches_oracle(gm, oracle_lib):
+    """20 000 particles, about 400 k edges: roughly 10 edge tiles per tile slot, 157 node tiles."""
+    n = 20_000
+    ref, mine = seeded_models(gm, oracle_lib, seed=0)
+    obs, nxt = scene.make_state(n, seed=1, n_rigid=n // 4)
+    nodes, edge_attr, ei, _ = oracle_features(oracle_lib).process_collate([(obs, nxt)])
+    with torch.no_grad():
+        want = ref(nodes, edge_attr, ei)
+    for impl, tol in ((2, ACC_TOL_TC), (1, ACC_TOL_SIMT)):
+        mine.impl = impl
+        got = mine(nodes, edge_attr, ei)                 # explicit edge_attr: the compatibility forward
+        err = rel_l2(got, want)
+        print(f"n={n} E={ei.shape[1]} impl={impl} explicit edge_attr rel_l2={err:.3e}")
+        assert err < tol
+        got, E = device_forward(gm, mine, obs, impl)     # on-the-fly features: the rollout's forward
+        err = rel_l2(got, want)
+        print(f"n={n} E={E} impl={impl} device graph rel_l2={err:.3e}")
+        assert E == ei.shape[1] and err < tol
+
+
+def test_forward_c3_matches_reference_golden(gm, oracle_lib):
+    """C3 (BASELINE.json configs[2]): 100 000 particles, about 2 M edges, about 53 tiles per tile slot -- the regime
+    of roofline_c3.  Checked against the unmodified reference's forward (tests/golden/c3_forward.npz, every 25th
+    node) and, on all nodes, against the fp32 CUDA-core path on the same device."""
+    g = load_golden("c3_forward")
+    n = int(g["n"])
+    _, mine = seeded_models(gm, oracle_lib, int(g["weights_seed"]))
+    obs, _ = scene.make_state(n, seed=0, n_rigid=0)
+    tc, E = device_forward(gm, mine, obs, 2)
+    assert E == int(g["n_edges"])
+    idx = torch.from_numpy(g["idx"].astype(np.int64))
+    err_ref = rel_l2(tc[idx], g["pred"])
+    simt, _ = device_forward(gm, mine, obs, 1)
+    err_simt_ref = rel_l2(simt[idx], g["pred"])
+    err_tc_simt = rel_l2(tc, simt)
+    print(f"C3 E={E}: tc vs reference {err_ref:.3e}, simt vs reference {err_simt_ref:.3e}, tc vs simt {err_tc_simt:.3e}")
+    assert err_ref < ACC_TOL_TC and err_tc_simt < ACC_TOL_TC
+    assert err_simt_ref < 10 * ACC_TOL_SIMT
+    assert abs(float(tc.norm()) / float(g["pred_norm"]) - 1.0) < 1e-3
+
+
+# ---------------------------------------------------------------------------------------------------------
+# batched candidates on the tensor-core path (the C4 plan)
+# ---------------------------------------------------------------------------------------------------------
+def _c2_setup(gm, oracle_lib, steps, n_cand):
+    n, n_rigid = 2000, scene.N_RIGID
+    ref, mine = seeded_models(gm, oracle_lib, seed=0)
+    obs, _ = scene.make_state(n, seed=0, n_rigid=n_rigid)
+    st = scene.sample_traj()
+    rng = np.random.RandomState(5)
+    rot = np.deg2rad(st[:steps, 0])[None] + np.cumsum(rng.randn(n_cand, steps) * 2e-3, axis=1)
+    ty = (st[:steps, 1] - st[0, 1])[None] + np.cumsum(rng.randn(n_cand, steps) * 2e-5, axis=1)
+    return ref, mine, obs, rot, ty
+
+
+@pytest.mark.parametrize("n_cand", [8, 64])
+def test_rollout_batched_candidates_tensor_path(gm, oracle_lib, n_cand):
+    """n_graphs = 8 / 64 x 2 000 particles on impl=2 (64: the C4 plan, 128 000 nodes, 2.56 M edges) against
+    single-candidate tensor-path plans and against the CPU oracle's rollout, 3 steps."""
+    steps = 3
+    ref, mine, obs, rot, ty = _c2_setup(gm, oracle_lib, steps, n_cand)
+    ga = make_graph_attr(gm)
+    plan = gm.Rollout(mine, ga, obs, rot=rot, ty=ty, ty_init=tuple(scene.TY_INIT), n_graphs=n_cand, impl=2,
+                      use_cuda_graph=True)
+    preds = []
+    for _ in range(steps):
+        plan.run(1)
+        preds.append(plan.pred.cpu().reshape(n_cand, 2000, 3).clone())
+    final = plan.obs.cpu().reshape(6, n_cand, 2000, 8)
+    picks = sorted({0, n_cand // 2 - 1, n_cand - 1})
+    feats = oracle_features(oracle_lib)
+    for c in picks:
+        single = gm.Rollout(mine, ga, obs, rot=rot[c], ty=ty[c], ty_init=tuple(scene.TY_INIT), impl=2,
+                            use_cuda_graph=False)
+        sp = []
+        for _ in range(steps):
+            single.run(1)
+            sp.append(single.pred.cpu().clone())
+        e_single = max(rel_l2(preds[i][c], sp[i]) for i in range(steps))
+        dpos = float((final[:, c] - single.obs.cpu()).abs().max())
+        print(f"n_graphs={n_cand} candidate {c}: batched vs single rel_l2={e_single:.3e} max|dx|={dpos:.3e}")
+        assert e_single < 2e-4 and dpos < 1e-6      # same arithmetic, different tile boundaries (carry splits)
+    for c in picks[::2]:
+        rec = []
+        traj = oracle_lib.rigid_body_trajectory(rot[c], ty[c], steps, scene.TY_INIT,
+                                                obs[-1, :scene.N_RIGID][:, scene.CART_IDX])
+        want = oracle_lib.rollout(ref, feats, (obs, None), traj, feats.stats, steps,
+                                  record=lambda i, d: rec.append(d["pred"].clone()))
+        e0 = rel_l2(preds[0][c], rec[0])
+        eall = max(rel_l2(preds[i][c], rec[i]) for i in range(steps))
+        dpos = float((final[:, c] - want).abs().max())
+        print(f"n_graphs={n_cand} candidate {c}: vs oracle step0 {e0:.3e} worst {eall:.3e} max|dx|={dpos:.3e}")
+        assert e0 < ACC_TOL_TC and eall < 5 * ACC_TOL_TC and dpos < 1e-6
+
+
+@pytest.mark.parametrize("impl", [1, 2])
+def test_rollout_rot_ty_matches_explicit_trajectory_both_paths(gm, oracle_lib, impl):
+    g = load_golden("rollout")
+    _, mine = seeded_models(gm, oracle_lib, int(g["weights_seed"]))
+    obs0 = torch.from_numpy(g["obs0"])
+    a = gm.Rollout(mine, make_graph_attr(gm), obs0, trajectory=torch.from_numpy(g["traj"]), impl=impl)
+    b = gm.Rollout(mine, make_graph_attr(gm), obs0, rot=g["rot"], ty=g["ty"], ty_init=tuple(g["ty_init"]), impl=impl)
+    fa, fb = a.run(int(g["horizon"])).cpu(), b.run(int(g["horizon"])).cpu()
+    assert float((fa - fb).abs().max()) < 1e-6
+
+
+@pytest.mark.parametrize("impl,tol", [(1, ACC_TOL_SIMT), (2, ACC_TOL_TC)])
+@pytest.mark.parametrize("cuda_graph", [False, True])
+def test_rollout_beyond_trajectory_end(gm, oracle_lib, impl, tol, cuda_graph):
+    """The reference quirk gnn_manip/utils/traj_utils.py:128-129 / 150-152: once the step index passes the end of the
+    control trajectory the control columns of the rigid rows become their POSITION and the rigid rows are no longer
+    overwritten (physics.cu apply_control / integrate, `step >= traj_steps`).  5-step trajectory, 9 steps."""
+    n, n_rigid, t_len, steps = 600, 200, 5, 9
+    ref, mine = seeded_models(gm, oracle_lib, seed=0)
+    obs, _ = scene.make_state(n, seed=3, n_rigid=n_rigid)
+    feats = oracle_features(oracle_lib)
+    st = scene.sample_traj()
+    rot, ty = np.deg2rad(st[:t_len, 0]), st[:t_len, 1] - st[0, 1]
+    traj = oracle_lib.rigid_body_trajectory(rot, ty, t_len, scene.TY_INIT, obs[-1, :n_rigid][:, scene.CART_IDX])
+    rec = []
+    want = oracle_lib.rollout(ref, feats, (obs, None), traj, feats.stats, steps,
+                              record=lambda i, d: rec.append((d["nodes"].clone(), d["pred"].clone())))
+    plan = gm.Rollout(mine, make_graph_attr(gm), obs, trajectory=traj, impl=impl, use_cuda_graph=cuda_graph)
+    errs = []
+    for i in range(steps):
+        plan.run(1)
+        errs.append(rel_l2(plan.pred.cpu(), rec[i][1]))
+        if i == t_len:        # first step past the end: control columns of the node features hold normalised positions
+            nodes = plan.graph()[4].cpu()
+            assert float((nodes[:n_rigid, 22:25] - rec[i][0][:n_rigid, 22:25]).abs().max()) < 1e-2
+            assert float(nodes[:n_rigid, 22:25].abs().min()) > 100.0
+    got = plan.obs.cpu()
+    print(f"impl={impl} graph={cuda_graph} per-step rel_l2 {[f'{e:.1e}' for e in errs]}")
+    assert max(errs[: t_len + 1]) < tol and max(errs) < 20 * tol
+    assert float((got - want).abs().max()) < 2e-6
+    assert torch.equal(got[..., :2], want[..., :2])
+
+
+# ---------------------------------------------------------------------------------------------------------
+# 300-step horizon at C2 size (BASELINE.json configs[1])
+# ---------------------------------------------------------------------------------------------------------
+# Free-running position RMSE of the sand particles against the unmodified reference's rollout, in units of conn_r.
+# The dynamics are discontinuous in the neighbour set, so two correct implementations drift apart once their graphs
+# differ; the bound is therefore stated per horizon (measured value x ~10 margin, see the print below).
+RMSE_BOUND_CONN_R = {10: 1e-4, 50: 5e-3, 150: 0.5, 300: 2.0}
+
+
+@pytest.mark.parametrize("impl", [2, 1])
+def test_rollout_c2_300_steps_rmse(gm, oracle_lib, impl):
+    """SURVEY.md section 8 row D gate (4): the bench's C2 rollout (2 000 particles, 828 rigid, sample_traj control
+    curve, seed-0 weights) free-running for 300 steps, compared at t = 10 / 50 / 150 / 300 with the reference's own
+    cma_objective loop (tests/golden/rollout_c2.npz, oracle/make_golden.py golden_rollout_c2)."""
+    g = load_golden("rollout_c2")
+    horizon, n_rigid = int(g["horizon"]), int(g["n_rigid"])
+    _, mine = seeded_models(gm, oracle_lib, int(g["weights_seed"]))
+    obs, _ = scene.make_state(2000, seed=0, n_rigid=n_rigid)
+    plan = gm.Rollout(mine, make_graph_attr(gm), obs, rot=g["rot"], ty=g["ty"], ty_init=tuple(scene.TY_INIT),
+                      impl=impl, use_cuda_graph=True)
+    marks = [int(t) for t in g["marks"]]
+    rmse, edges = {}, {}
+    done = 0
+    for t in marks:
+        plan.run(t - done)
+        done = t
+        sand = plan.obs[-1, n_rigid:, 2:5].cpu()          # state entering step t
+        rmse[t] = float(((sand - torch.from_numpy(g[f"sand_{t}"])) ** 2).mean().sqrt()) / scene.CONN_R
+        edges[t] = int(plan.graph()[3])                   # edge count of step t - 1
+    ref_edges = g["n_edges"]
+    print(f"impl={impl} free-running RMSE / conn_r:", {k: f"{v:.3e}" for k, v in rmse.items()},
+          "edges (ours, step t-1):", edges, "reference:", {t: int(ref_edges[t - 1]) for t in marks},
+          "reference mean edges/step:", float(ref_edges.mean()))
+    assert edges[10] == int(ref_edges[9])
+    for t in marks:
+        assert rmse[t] < RMSE_BOUND_CONN_R[t], f"t={t}: RMSE {rmse[t]:.3e} conn_r"
