@@ -382,6 +382,128 @@ class TrajectoryParam:
         return rot, ty
 
 
+def pchip_slopes(xk, yk):
+    """scipy.interpolate.PchipInterpolator._find_derivatives / _edge_case (scipy 1.18, _cubic.py; the reference
+    calls scipy.interpolate.pchip_interpolate at traj_utils.py:413-414; scipy is unpinned in environment.yml)."""
+    hk = xk[1:] - xk[:-1]
+    mk = (yk[1:] - yk[:-1]) / hk
+    n = len(yk)
+    if n == 2:
+        return np.array([mk[0], mk[0]])
+    dk = np.zeros(n)
+    for k in range(1, n - 1):
+        m0, m1 = mk[k - 1], mk[k]
+        if np.sign(m0) != np.sign(m1) or m0 == 0.0 or m1 == 0.0:
+            dk[k] = 0.0
+        else:
+            w1 = 2 * hk[k] + hk[k - 1]
+            w2 = hk[k] + 2 * hk[k - 1]
+            dk[k] = 1.0 / ((w1 / m0 + w2 / m1) / (w1 + w2))
+
+    def edge(h0, h1, m0, m1):
+        d = ((2 * h0 + h1) * m0 - h0 * m1) / (h0 + h1)
+        if np.sign(d) != np.sign(m0):
+            return 0.0
+        if np.sign(m0) != np.sign(m1) and abs(d) > 3.0 * abs(m0):
+            return 3.0 * m0
+        return d
+    dk[0] = edge(hk[0], hk[1], mk[0], mk[1])
+    dk[-1] = edge(hk[-1], hk[-2], mk[-1], mk[-2])
+    return dk
+
+
+def pchip_eval(xk, yk, xq):
+    """CubicHermiteSpline coefficients (_cubic.py) and PPoly evaluation (_ppoly evaluate_poly1: the power basis,
+    res = c3 + c2 s + c1 s^2 + c0 s^3 with s^k accumulated by repeated multiplication)."""
+    xk = np.asarray(xk, dtype=np.float64)
+    yk = np.asarray(yk, dtype=np.float64)
+    dk = pchip_slopes(xk, yk)
+    dx = xk[1:] - xk[:-1]
+    slope = (yk[1:] - yk[:-1]) / dx
+    t = (dk[:-1] + dk[1:] - 2 * slope) / dx
+    c0, c1, c2, c3 = t / dx, (slope - dk[:-1]) / dx - t, dk[:-1], yk[:-1]
+    out = np.empty(len(xq))
+    for q, x in enumerate(xq):
+        i = min(max(int(np.searchsorted(xk, x, side="right")) - 1, 0), len(xk) - 2)
+        s = x - xk[i]
+        res, z = 0.0, 1.0
+        for c in (c3[i], c2[i], c1[i], c0[i]):
+            res = res + c * z * 1.0
+            z = z * s
+        out[q] = res
+    return out
+
+
+class PchipParam:
+    """InterpolatedCMAsolver (traj_utils.py:288-452): knots every ``nr_traj_points`` steps, parameters = scaled
+    offsets of the knots from (rx_init, 0), curves by pchip interpolation; with the ctor quirk
+    scale_ty = (ty_init[0] - 0.3) / scale_rot (traj_utils.py:61)."""
+
+    def __init__(self, rx_init_deg, ty_init, scale_rot, max_rot_deg, max_ty, total_steps, traj_points):
+        self.rx_init = np.deg2rad(rx_init_deg)
+        self.ty_init = ty_init
+        self.scale_rot = scale_rot
+        self.scale_ty = (ty_init[0] - 0.3) / scale_rot
+        self.max_rot = np.deg2rad(max_rot_deg)
+        self.max_ty = max_ty
+        self.horizon = total_steps
+        self.nr = traj_points                       # steps between knots (self.nr_traj_points)
+        self.n_knots = int(total_steps / traj_points)   # self.traj_points
+
+    def x0_from_sample(self, sample_traj):
+        """set_sample_traj (traj_utils.py:296-303)."""
+        pts = sample_traj[list(range(self.nr, sample_traj.shape[0], self.nr))]
+        return np.concatenate(((np.deg2rad(pts[:, 0]) - self.rx_init) / self.scale_rot,
+                               (pts[:, 1] - self.ty_init[0]) / self.scale_ty))
+
+    def interpolate(self, x):
+        """interpolate_trajectory (traj_utils.py:393-416), type_interp='pchip'."""
+        x = np.asarray(x, dtype=np.float64)
+        m = len(x) // 2
+        rot_pts = np.concatenate(([self.rx_init], self.rx_init + x[:m] * self.scale_rot))
+        ty_pts = np.concatenate(([0.0], x[m:] * self.scale_ty))
+        xk = np.arange(0, self.horizon + 1, self.nr).astype(np.float64)
+        xq = np.arange(self.horizon).astype(np.float64)
+        return pchip_eval(xk, rot_pts, xq), pchip_eval(xk, ty_pts, xq)
+
+    def terms(self, x):
+        """(vel_loss, acc_loss, interp_loss) of compute_loss (traj_utils.py:353-373, 418-452)."""
+        rot, ty = self.interpolate(x)
+        actions = np.stack((rot, ty), axis=1)
+        vel = actions[1:] - actions[:-1]
+        acc = actions[2:] - 2 * actions[1:-1] + actions[:-2]
+        vel_loss = np.sqrt(np.sum((vel / np.array([1e-2, 4e-4])) ** 2))
+        acc_loss = np.sqrt(np.sum((acc / np.array([2.2e-4, 1.45e-4])) ** 2))
+        x = np.asarray(x, dtype=np.float64)
+        r, t = x[:self.n_knots] * self.scale_rot, x[self.n_knots:] * self.scale_ty
+        ineq = max((np.abs(r[1:] - r[:-1]) - self.max_rot * self.nr).max(),
+                   (np.abs(t[1:] - t[:-1]) - self.max_ty * self.nr).max())
+        return vel_loss, acc_loss, float(np.exp(ineq))
+
+    def ineq_constraint(self, x):
+        """traj_utils.py:375-391."""
+        x = np.asarray(x, dtype=np.float64)
+        actions = np.zeros((self.n_knots + 1, 2))
+        actions[1:, 0] = x[:self.n_knots] * self.scale_rot
+        actions[1:, 1] = x[self.n_knots:] * self.scale_ty
+        vel = actions[1:] - actions[:-1]
+        up = np.abs(vel) - np.array([self.max_rot * self.nr, self.max_ty * self.nr])
+        return np.concatenate((up[:, 0] / self.scale_rot, up[:, 1] / self.scale_ty))
+
+
+def increments_terms(param, x, rotation_limit=2.8973):
+    """TrajectoryCMAsolver loss terms (traj_utils.py:230-246, 263-285): (vel_loss, acc_loss, bound penalty)."""
+    rot, ty = param.interpolate(np.asarray(x, dtype=np.float64))
+    actions = np.stack((np.array(rot), np.array(ty)), axis=1)
+    vel = actions[1:] - actions[:-1]
+    acc = actions[2:] - 2 * actions[1:-1] + actions[:-2]
+    div = np.array([param.max_rot, param.max_ty])
+    pen = 0.0
+    if actions[:, 0].max() > param.rx_init + rotation_limit or actions[:, 0].min() < param.rx_init - rotation_limit:
+        pen = 20.0
+    return np.sqrt(np.sum((vel / div) ** 2)), np.sqrt(np.sum((acc / div) ** 2)), pen
+
+
 def rollout(model, feats, state, trajectory, stats, horizon, record=None, teacher=None):
     """The loop of CMAESolver.cma_objective (traj_utils.py:119-152) == compute_rollout
     (rollout_utils.py:38-65) without the loss tail.  ``state`` = (obs [k,N,D], next_pos) is cloned.

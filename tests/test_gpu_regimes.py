@@ -192,8 +192,13 @@ def test_rollout_beyond_trajectory_end(gm, oracle_lib, impl, tol, cuda_graph):
 # ---------------------------------------------------------------------------------------------------------
 # Free-running position RMSE of the sand particles against the unmodified reference's rollout, in units of conn_r.
 # The dynamics are discontinuous in the neighbour set, so two correct implementations drift apart once their graphs
-# differ; the bound is therefore stated per horizon (measured value x ~10 margin, see the print below).
-RMSE_BOUND_CONN_R = {10: 1e-4, 50: 5e-3, 150: 0.5, 300: 2.0}
+# differ; the bound is therefore stated per horizon, about 10 x the measured value.  Measured on B200 (round 2):
+#   tensor path (bf16x3)   2.8e-6 / 6.2e-5 / 1.9e-3 / 8.0e-2 conn_r at t = 10 / 50 / 150 / 300
+#   fp32 CUDA-core path    8.6e-7 / 1.3e-5 / 6.0e-4 / 4.6e-2 conn_r  (the same arithmetic as the CPU reference up to
+#                          summation order, and it drifts almost as far: the horizon-300 figure measures the chaos of
+#                          the rollout, not the precision of the kernels)
+# Edge counts of the two rollouts: 39 945 / 37 341 / 22 566 / 18 781 against 39 945 / 37 339 / 22 568 / 18 775.
+RMSE_BOUND_CONN_R = {10: 3e-5, 50: 6e-4, 150: 2e-2, 300: 0.8}
 
 
 @pytest.mark.parametrize("impl", [2, 1])
