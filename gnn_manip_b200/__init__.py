@@ -13,6 +13,8 @@ from .graph_networks import (EdgeModel, GraphIndependent, GraphNetwork, Interact
 from .collate_utils import (GraphAttributes, GraphBoundedMultimaterial,  # noqa: F401
                             GraphBoundedMultimaterialControl, GraphSimple)
 from .rollout_utils import Rollout, compute_rollout, get_position_from_prediction  # noqa: F401
+from .traj_utils import (CMAESolver, InterpolatedCMAsolver, TrajectoryCMAsolver,  # noqa: F401
+                         sinkhorn_divergence)
 from .utils import (compute_acceleration, get_connectivity, get_edges_displacement,  # noqa: F401
                     get_nodes_vel, radius_graph)
 

@@ -41,6 +41,17 @@ class gm_rollout_desc(ctypes.Structure):
     ]
 
 
+class gm_traj_param(ctypes.Structure):
+    _fields_ = [
+        ("kind", c_int32), ("horizon", c_int32), ("n_points", c_int32), ("knot_stride", c_int32),
+        ("rx_init", c_double), ("scale_rot", c_double), ("scale_ty", c_double),
+        ("max_rot", c_double), ("max_ty", c_double), ("rotation_limit", c_double), ("bound_penalty", c_double),
+        ("vel_div", c_double * 2), ("acc_div", c_double * 2),
+    ]
+
+
+GM_TRAJ_INCREMENTS, GM_TRAJ_PCHIP = 0, 1
+
 # name -> (restype, argtypes); every symbol of include/gnn_manip_b200.h
 SIGNATURES = {
     "gm_version": (ctypes.c_int, []),
@@ -81,6 +92,13 @@ SIGNATURES = {
     "gm_rollout_graph": (ctypes.c_int, [c_void_p] + [POINTER(c_void_p)] * 5),
     "gm_rollout_kernel_launches_per_step": (c_int64, [c_void_p]),
     "gm_rollout_destroy": (None, [c_void_p]),
+    "gm_traj_interpolate": (ctypes.c_int, [POINTER(gm_traj_param), c_void_p, c_int32, c_void_p, c_void_p, c_void_p,
+                                           c_void_p]),
+    "gm_rigid_trajectory": (ctypes.c_int, [c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_int32, POINTER(c_float),
+                                           c_void_p, c_void_p]),
+    "gm_sinkhorn_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32]),
+    "gm_sinkhorn_divergence": (ctypes.c_int, [c_void_p, c_int32, c_int64, c_void_p, c_int32, c_void_p, c_int32, c_int32,
+                                              c_double, c_double, c_double, c_void_p, c_void_p, c_size_t, c_void_p]),
     "gm_debug_stamps": (ctypes.c_int, [c_void_p, c_int32]),
     "gm_selftest_gemm": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),
     "gm_selftest_gemm_ts": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),

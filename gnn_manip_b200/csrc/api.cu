@@ -1,4 +1,5 @@
 // C ABI (include/gnn_manip_b200.h): model packing, forward orchestration, rollout plan + CUDA graph.
+#include <math.h>
 #include <stdarg.h>
 #include <string.h>
 #include <new>
@@ -11,6 +12,8 @@
 #include "physics.cuh"
 #include "radius_graph.cuh"
 #include "scan.cuh"
+#include "sinkhorn.cuh"
+#include "traj.cuh"
 
 namespace gm {
 
@@ -829,6 +832,51 @@ void gm_rollout_destroy(gm_rollout* r) {
   if (r->ev_join) cudaEventDestroy(r->ev_join);
   if (r->side) cudaStreamDestroy(r->side);
   delete r;
+}
+
+int gm_traj_interpolate(const gm_traj_param* q, const double* x, int32_t n_cand, double* rot, double* ty,
+                        double* terms, void* stream) {
+  GM_REQUIRE(q != nullptr && x != nullptr && rot != nullptr && ty != nullptr, "gm_traj_interpolate: NULL argument");
+  TrajParams p;
+  p.kind = q->kind; p.horizon = q->horizon; p.n_points = q->n_points; p.knot_stride = q->knot_stride;
+  p.rx_init = q->rx_init; p.scale_rot = q->scale_rot; p.scale_ty = q->scale_ty;
+  p.max_rot = q->max_rot; p.max_ty = q->max_ty;
+  p.rotation_limit = q->rotation_limit; p.bound_penalty = q->bound_penalty;
+  for (int i = 0; i < 2; ++i) { p.vel_div[i] = q->vel_div[i]; p.acc_div[i] = q->acc_div[i]; }
+  return traj_interpolate(p, x, n_cand, rot, ty, terms, (cudaStream_t)stream);
+}
+
+int gm_rigid_trajectory(const double* rot, const double* ty, int32_t n_cand, int32_t steps, const float* rigid_init,
+                        int32_t n_rigid, const float* ty_init_host, float* out, void* stream) {
+  GM_REQUIRE(ty_init_host != nullptr, "gm_rigid_trajectory: ty_init is NULL");
+  return rigid_trajectory(rot, ty, n_cand, steps, rigid_init, n_rigid, ty_init_host, out, (cudaStream_t)stream);
+}
+
+size_t gm_sinkhorn_workspace_bytes(int32_t n_batch, int32_t n, int32_t m) {
+  if (n_batch <= 0 || n <= 0 || m <= 0) return 0;
+  return sinkhorn_workspace_bytes(n_batch, n, m);
+}
+
+int gm_sinkhorn_divergence(const float* x, int32_t x_stride, int64_t x_batch_stride, const int32_t* x_idx, int32_t n,
+                           const float* y, int32_t m, int32_t n_batch, double blur, double scaling,
+                           double diameter_max, float* loss, void* workspace, size_t workspace_bytes, void* stream) {
+  GM_REQUIRE(x != nullptr && y != nullptr && loss != nullptr, "gm_sinkhorn_divergence: NULL argument");
+  GM_REQUIRE(n > 0 && m > 0 && n_batch > 0 && x_stride >= 3, "gm_sinkhorn_divergence: bad sizes");
+  GM_REQUIRE(blur > 0.0 && scaling > 0.0 && scaling < 1.0 && diameter_max > 0.0,
+             "gm_sinkhorn_divergence: blur=%g scaling=%g diameter_max=%g", blur, scaling, diameter_max);
+  Arena a(workspace, workspace_bytes);
+  SinkhornWs ws;
+  sinkhorn_carve(a, n_batch, n, m, ws);
+  if (!a.ok || workspace == nullptr) {
+    set_error("gm_sinkhorn_divergence: workspace too small (%zu < %zu bytes)", workspace_bytes, a.off);
+    return GM_ERR_WORKSPACE;
+  }
+  // schedule length for the largest diameter: [d^2] + arange(2 log d, 2 log blur, 2 log scaling) + [blur^2]
+  int iters = 2;
+  if (diameter_max > blur) iters += (int)ceil(log(diameter_max / blur) / -log(scaling));
+  if (iters > kSinkMaxEps) iters = kSinkMaxEps;
+  return sinkhorn_divergence(x, x_stride, x_batch_stride, x_idx, n, y, m, n_batch, blur, scaling, iters, loss, ws,
+                             (cudaStream_t)stream);
 }
 
 #ifdef GM_TRACE

@@ -9,6 +9,7 @@
 // All arithmetic is IEEE fp32 with the reference's operation order and *no* FMA contraction
 // (true division, sqrt.rn), so node features and the integrator are bit-identical to the CPU
 // reference; the edge norm uses the fused accumulation torch.norm performs on CPU.
+#include <string.h>
 #include "common.cuh"
 #include "physics.cuh"
 
@@ -77,6 +78,20 @@ __device__ __forceinline__ void rigid_target(const RolloutParams& rp, int g, int
   const float w1 = __fadd_rn(__fadd_rn(__fmul_rn(c, q1), __fmul_rn(-s, q2)), t1);
   const float w2 = __fadd_rn(__fadd_rn(__fmul_rn(s, q1), __fmul_rn(c, q2)), rp.ty_init[2]);
   out[0] = w0; out[1] = w2; out[2] = w1;
+}
+
+// get_rigid_body_trajectory_from_diff (traj_utils.py:87-103): the rigid-particle targets of every candidate and step,
+// materialised (the rollout plan itself evaluates rigid_target on the fly; this is the reference-shaped output).
+__global__ void rigid_trajectory_kernel(RolloutParams rp, int steps, float* __restrict__ out) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)rp.n_graphs * steps * rp.n_rigid;
+  if (idx >= total) return;
+  const int r = (int)(idx % rp.n_rigid);
+  const int step = (int)((idx / rp.n_rigid) % steps);
+  const int g = (int)(idx / ((long long)rp.n_rigid * steps));
+  float tgt[3];
+  rigid_target(rp, g, r, step, tgt);
+  out[idx * 3 + 0] = tgt[0]; out[idx * 3 + 1] = tgt[1]; out[idx * 3 + 2] = tgt[2];
 }
 
 // Step (1) of the loop body: control columns of the rigid particles (traj_utils.py:126-135).
@@ -184,6 +199,22 @@ int edge_features(const float* pos, int stride, const int* send, const int* recv
                                                                     max_edges, conn_r, (float4*)edge_attr);
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("edge_features_kernel");
+  return GM_OK;
+}
+
+int rigid_trajectory(const double* rot, const double* ty, int n_cand, int steps, const float* rigid_init, int n_rigid,
+                     const float ty_init[3], float* out, cudaStream_t stream) {
+  GM_REQUIRE(rot != nullptr && ty != nullptr && rigid_init != nullptr && out != nullptr, "rigid_trajectory: NULL argument");
+  GM_REQUIRE(n_cand > 0 && steps > 0 && n_rigid > 0, "rigid_trajectory: bad sizes");
+  RolloutParams rp;
+  memset(&rp, 0, sizeof(rp));
+  rp.n_graphs = n_cand; rp.n_rigid = n_rigid; rp.traj_steps = steps;
+  rp.rot = rot; rp.ty = ty; rp.rigid_init = rigid_init;
+  for (int i = 0; i < 3; ++i) rp.ty_init[i] = ty_init[i];
+  const long long total = (long long)n_cand * steps * n_rigid;
+  rigid_trajectory_kernel<<<ceil_div(total, 256), 256, 0, stream>>>(rp, steps, out);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("rigid_trajectory_kernel");
   return GM_OK;
 }
 

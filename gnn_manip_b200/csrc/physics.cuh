@@ -35,6 +35,8 @@ int node_features(const float* obs, int k, int n, int D, const PhysParams& p, fl
 int edge_features(const float* pos, int stride, const int* send, const int* recv, const int* n_edges_dev,
                   int max_edges, float conn_r, float* edge_attr, cudaStream_t stream);
 int apply_control(float* obs, const RolloutParams& rp, cudaStream_t stream);
+int rigid_trajectory(const double* rot, const double* ty, int n_cand, int steps, const float* rigid_init, int n_rigid,
+                     const float ty_init[3], float* out, cudaStream_t stream);
 int integrate(float* obs, const float* pred, const RolloutParams& rp, float* next_pos_out, cudaStream_t stream);
 
 #ifdef __CUDACC__

@@ -65,7 +65,10 @@ class Rollout:
         d.impl = int(model.impl if impl is None else impl)
         d.phys = graph_attr.phys()
         d.k, d.D, d.n_per_graph, d.n_graphs = k, D, n, self.n_graphs
-        d.max_neighbours = int(graph_attr.max_neighbours)
+        # collate_utils.py:34: the noise-free path (the only one a rollout takes) calls get_connectivity without
+        # max_neighbours, so the cap is utils.py:64's default 20 whatever the graph_attr was built with
+        d.max_neighbours = int(graph_attr._simple_max_neighbours if graph_attr.noise_std is None
+                               else graph_attr.max_neighbours)
         d.n_rigid = self.n_rigid
         d.rigid_idx = self.rigid_idx.data_ptr() if self.n_rigid else None
         d.traj_steps = 0
@@ -88,6 +91,7 @@ class Rollout:
             r64, t64 = r64.contiguous().to(dev), t64.contiguous().to(dev)
             init = obs0[-1, rigid.long()][:, cart].contiguous()
             self._keep += [r64, t64, init]
+            self.rot_dev, self.ty_dev, self.rigid_init = r64, t64, init      # [n_graphs, T] fp64 control curves
             d.rot, d.ty, d.rigid_init, d.traj_steps = r64.data_ptr(), t64.data_ptr(), init.data_ptr(), r64.shape[1]
         d.ty_init[:] = [float(x) for x in ty_init]
         d.obs = self.obs.data_ptr()

@@ -203,6 +203,56 @@ int gm_rollout_graph(const gm_rollout* plan, const int32_t** nbr, const int32_t*
 int64_t gm_rollout_kernel_launches_per_step(const gm_rollout* plan);
 void gm_rollout_destroy(gm_rollout* plan);
 
+/* ---- Row N2: CMA-ES trajectory parametrisations (gnn_manip/utils/traj_utils.py) ------------------------------
+ * kind GM_TRAJ_INCREMENTS  TrajectoryCMAsolver.interpolate_trajectory (traj_utils.py:206-228): x holds per-step
+ *                          increments, scaled, clipped to +-max_rot / +-max_ty and accumulated from (rx_init, 0);
+ *                          n_points = horizon - 1 parameters per curve.
+ * kind GM_TRAJ_PCHIP       InterpolatedCMAsolver.interpolate_trajectory (traj_utils.py:393-416): x holds the knots
+ *                          after the first (one every knot_stride steps, n_points * knot_stride == horizon), scaled
+ *                          and offset from (rx_init, 0), interpolated like scipy.interpolate.pchip_interpolate.
+ * x [n_cand, 2 * n_points] (rotation parameters first, then translation, as the reference's search vector), fp64.
+ * rot / ty [n_cand, horizon] fp64 radians / metres: exactly the buffers a rollout plan reads (gm_rollout_desc.rot /
+ * .ty), so a population's candidates go from the optimiser's vectors to rigid-particle targets without leaving the
+ * device.  terms (optional) [n_cand, 3]: the curve regularisers of compute_loss -- ||vel / vel_div||, ||acc /
+ * acc_div|| (compute_vel_acc / compute_vel_loss / compute_acc_loss, traj_utils.py:161-165, 230-246, 353-373) and
+ * the penalty term (kind 0: compute_boundaries_penalty :263-274; kind 1: compute_vel_noninterp :418-436). */
+enum gm_traj_kind { GM_TRAJ_INCREMENTS = 0, GM_TRAJ_PCHIP = 1 };
+typedef struct gm_traj_param {
+  int32_t kind;
+  int32_t horizon;
+  int32_t n_points;
+  int32_t knot_stride;        /* kind 1 only */
+  double rx_init;             /* radians */
+  double scale_rot, scale_ty;
+  double max_rot, max_ty;     /* radians, metres */
+  double rotation_limit;      /* kind 0: penalty when the rotation leaves rx_init +- rotation_limit (2.8973) */
+  double bound_penalty;       /* kind 0: 20.0 */
+  double vel_div[2], acc_div[2];
+} gm_traj_param;
+int gm_traj_interpolate(const gm_traj_param* param_host, const double* x, int32_t n_cand, double* rot, double* ty,
+                        double* terms, void* stream);
+
+/* get_rigid_body_trajectory_from_diff / compute_particles_tmatrix (traj_utils.py:87-103, 167-194) for a whole
+ * population: out [n_cand, steps, n_rigid, 3] fp32 rigid-particle targets from the control curves rot / ty
+ * [n_cand, steps] (fp64) and the rigid particles' initial positions rigid_init [n_rigid, 3]. */
+int gm_rigid_trajectory(const double* rot, const double* ty, int32_t n_cand, int32_t steps, const float* rigid_init,
+                        int32_t n_rigid, const float* ty_init_host, float* out, void* stream);
+
+/* ---- Row N1: batched Sinkhorn divergence (the Wasserstein term of compute_loss, traj_utils.py:276, 439) --------
+ * loss[b] = S_eps(x_b, y) for uniform point clouds, p = 2, cost |x - y|^2 / 2, eps = blur^2, epsilon scaling with
+ * ratio `scaling` from the clouds' joint diameter, symmetrised updates, debiased -- the tensorized algorithm of
+ * geomloss.SamplesLoss(loss="sinkhorn", p=2, blur=.05) (traj_utils.py:69; geomloss defaults scaling=.5).  geomloss
+ * is an unpinned third-party dependency absent from the reference checkout: PARITY UNPINNED (oracle: the fp64
+ * numpy statement of the same algorithm, oracle/restate.py sinkhorn_divergence).
+ *   x: point i of candidate b at x + b * x_batch_stride + (x_idx ? x_idx[i] : i) * x_stride, 3 floats -- e.g. the
+ *      sand rows of the last frame of a rollout plan's obs, read in place
+ *   y [m, 3]: target cloud shared by the population;  diameter_max: an upper bound of any candidate's joint
+ *      bounding-box diagonal (sizes the fixed number of launched iterations; shorter schedules idle through) */
+size_t gm_sinkhorn_workspace_bytes(int32_t n_batch, int32_t n, int32_t m);
+int gm_sinkhorn_divergence(const float* x, int32_t x_stride, int64_t x_batch_stride, const int32_t* x_idx, int32_t n,
+                           const float* y, int32_t m, int32_t n_batch, double blur, double scaling,
+                           double diameter_max, float* loss, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Debug aid: phase timestamps (clock64) recorded by CTA 0 of the instrumented kernels; only in -DGM_STAMPS builds
  * (returns GM_STATUS_UNSUPPORTED otherwise).  out_host: host array of n <= 64 values. */
 int gm_debug_stamps(unsigned long long* out_host, int32_t n);

@@ -504,6 +504,54 @@ def increments_terms(param, x, rotation_limit=2.8973):
     return np.sqrt(np.sum((vel / div) ** 2)), np.sqrt(np.sum((acc / div) ** 2)), pen
 
 
+# --------------------------------------------------------------------------------------
+# N1  Sinkhorn divergence (objective tail of cma_objective) -- PARITY UNPINNED
+# --------------------------------------------------------------------------------------
+
+
+def sinkhorn_epsilon_schedule(diameter, blur, scaling, p=2):
+    """geomloss sinkhorn_divergence.epsilon_schedule."""
+    return ([diameter ** p] + [float(np.exp(e)) for e in
+                               np.arange(p * np.log(diameter), p * np.log(blur), p * np.log(scaling))] + [blur ** p])
+
+
+def sinkhorn_divergence(x, y, blur=0.05, scaling=0.5, dtype=np.float64):
+    """geomloss.SamplesLoss(loss="sinkhorn", p=2, blur=.05)(x, y) for uniform weights, restated in numpy from the
+    published tensorized algorithm (geomloss/sinkhorn_samples.py: softmin_tensorized, sinkhorn_tensorized;
+    geomloss/sinkhorn_divergence.py: max_diameter, epsilon_schedule, sinkhorn_loop, sinkhorn_cost).  The reference
+    calls it at traj_utils.py:276 / :439 (constructed at :69).  geomloss is an unpinned pip dependency
+    (environment.yml:25) that is not installed here and not vendored in the reference: PARITY UNPINNED.  The one
+    deliberate difference: the cost |x-y|^2/2 is formed from coordinate differences (geomloss expands it as
+    |x|^2 - 2 x.y + |y|^2 in fp32, which loses about three digits for points 1e-2 apart at |x| ~ 0.5)."""
+    from scipy.special import logsumexp
+    x = np.asarray(x, dtype=dtype)
+    y = np.asarray(y, dtype=dtype)
+    n, m = len(x), len(y)
+
+    def cost(a, b):
+        d = a[:, None, :] - b[None, :, :]
+        return 0.5 * (d * d).sum(-1)
+    c_xy, c_yx, c_xx, c_yy = cost(x, y), cost(y, x), cost(x, x), cost(y, y)
+    both = np.concatenate((x, y)).astype(np.float32)
+    diameter = float(np.linalg.norm(both.max(0) - both.min(0)))
+    eps_list = sinkhorn_epsilon_schedule(diameter, blur, scaling)
+    a_log, b_log = np.full(n, -np.log(n), dtype=dtype), np.full(m, -np.log(m), dtype=dtype)
+
+    def softmin(eps, c, h):
+        return -eps * logsumexp(h[None, :] - c / eps, axis=1)
+    eps = eps_list[0]
+    g_ab, f_ba = softmin(eps, c_yx, a_log), softmin(eps, c_xy, b_log)
+    f_aa, g_bb = softmin(eps, c_xx, a_log), softmin(eps, c_yy, b_log)
+    for eps in eps_list:
+        ft_ba, gt_ab = softmin(eps, c_xy, b_log + g_ab / eps), softmin(eps, c_yx, a_log + f_ba / eps)
+        ft_aa, gt_bb = softmin(eps, c_xx, a_log + f_aa / eps), softmin(eps, c_yy, b_log + g_bb / eps)
+        f_ba, g_ab = 0.5 * (f_ba + ft_ba), 0.5 * (g_ab + gt_ab)
+        f_aa, g_bb = 0.5 * (f_aa + ft_aa), 0.5 * (g_bb + gt_bb)
+    f_ba, g_ab = softmin(eps, c_xy, b_log + g_ab / eps), softmin(eps, c_yx, a_log + f_ba / eps)
+    f_aa, g_bb = softmin(eps, c_xx, a_log + f_aa / eps), softmin(eps, c_yy, b_log + g_bb / eps)
+    return float(np.mean(f_ba - f_aa) + np.mean(g_ab - g_bb))
+
+
 def rollout(model, feats, state, trajectory, stats, horizon, record=None, teacher=None):
     """The loop of CMAESolver.cma_objective (traj_utils.py:119-152) == compute_rollout
     (rollout_utils.py:38-65) without the loss tail.  ``state`` = (obs [k,N,D], next_pos) is cloned.
