@@ -12,7 +12,9 @@ from .graph_networks import (EdgeModel, GraphIndependent, GraphNetwork, Interact
                              NodeModel)
 from .collate_utils import (GraphAttributes, GraphBoundedMultimaterial,  # noqa: F401
                             GraphBoundedMultimaterialControl, GraphSimple)
-from .rollout_utils import Rollout, compute_rollout, get_position_from_prediction  # noqa: F401
+from .rollout_utils import (Rollout, compute_rollout, get_position_from_prediction, perform_prediction,  # noqa: F401
+                            rollout_final_state)
+from .coffee_dataset import CoffeeDataset, CoffeeTestDataset, read_metadata, save_as_csv  # noqa: F401
 from .traj_utils import (CMAESolver, InterpolatedCMAsolver, TrajectoryCMAsolver,  # noqa: F401
                          sinkhorn_divergence)
 from .utils import (compute_acceleration, get_connectivity, get_edges_displacement,  # noqa: F401

@@ -89,6 +89,7 @@ SIGNATURES = {
     "gm_rollout_create": (ctypes.c_int, [POINTER(c_void_p), POINTER(gm_rollout_desc), c_void_p, c_size_t, c_void_p]),
     "gm_rollout_run": (ctypes.c_int, [c_void_p, c_int32, c_void_p]),
     "gm_rollout_reset": (ctypes.c_int, [c_void_p, c_int32, c_void_p]),
+    "gm_rollout_step_profile": (ctypes.c_int, [c_void_p, c_void_p, POINTER(c_float), POINTER(c_int32)]),
     "gm_rollout_graph": (ctypes.c_int, [c_void_p] + [POINTER(c_void_p)] * 5),
     "gm_rollout_kernel_launches_per_step": (c_int64, [c_void_p]),
     "gm_rollout_destroy": (None, [c_void_p]),

@@ -31,6 +31,30 @@ int cuda_fail(cudaError_t e, const char* what) {
   return GM_ERR_CUDA;
 }
 
+thread_local Profiler* g_profiler = nullptr;
+int Profiler::mark(int c) {
+  if (n >= kMax) { set_error("profiler: more than %d marks", kMax); return GM_ERR_INVALID; }
+  GM_CUDA(cudaEventCreate(&ev[n]));
+  GM_CUDA(cudaEventRecord(ev[n], st));
+  cls[n++] = c;
+  return GM_OK;
+}
+int Profiler::finish(float* ms_by_phase, int* launches_by_phase) {
+  cudaError_t ce = cudaStreamSynchronize(st);
+  for (int c = 0; c < kProfCount; ++c) { ms_by_phase[c] = 0.f; launches_by_phase[c] = 0; }
+  if (ce == cudaSuccess) {
+    for (int i = 0; i + 1 < n; ++i) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, ev[i], ev[i + 1]);
+      if (cls[i] >= 0 && cls[i] < kProfCount) { ms_by_phase[cls[i]] += ms; launches_by_phase[cls[i]] += 1; }
+    }
+  }
+  for (int i = 0; i < n; ++i) cudaEventDestroy(ev[i]);
+  n = 0;
+  if (ce != cudaSuccess) return cuda_fail(ce, "profiler sync");
+  return GM_OK;
+}
+
 namespace {
 
 __global__ void transpose_kernel(const float* __restrict__ w, int rows, int cols, float* __restrict__ wt) {
@@ -256,26 +280,10 @@ int forward_simt(const gm_model* m, const float* nodes, const float* edge_attr, 
   return GM_OK;
 }
 
-// per-kernel-class CUDA-event timing of one forward (gm_model_forward_profile): class 0 enc_edge, 1 enc_node,
-// 2 mp_edge, 3 mp_node(+decoder)
-struct FwdProfile {
-  std::vector<cudaEvent_t> ev;
-  std::vector<int> cls;
-  cudaStream_t st;
-  int mark(int c) {
-    cudaEvent_t e;
-    GM_CUDA(cudaEventCreate(&e));
-    GM_CUDA(cudaEventRecord(e, st));
-    ev.push_back(e);
-    cls.push_back(c);
-    return GM_OK;
-  }
-};
-
 int forward_tc(const gm_model* m, const float* nodes, const float* edge_attr, const float* pos, int pos_stride,
                float conn_r, int n_nodes, int max_edges, const int* n_edges_dev, const int* recv_ptr,
                const int* esend, const int* erecv, const int* eref, float* pred, const FwdWs& w,
-               cudaStream_t st, FwdProfile* prof = nullptr, cudaEvent_t enc_node_done = nullptr) {
+               cudaStream_t st, cudaEvent_t enc_node_done = nullptr) {
   // enc_node_done: the caller already launched the node encoder on another stream (it needs only the node features,
   // so a rollout runs it beside the graph build); the first edge step joins on the event instead.
   GM_REQUIRE(m->tc_ok, "model shape (hidden=%d, num_layers=%d) is not covered by the tcgen05 kernels", m->hidden,
@@ -283,27 +291,25 @@ int forward_tc(const gm_model* m, const float* nodes, const float* edge_attr, co
   TcGraph g{n_edges_dev, max_edges, n_nodes, esend, erecv, recv_ptr};
   TcBuffers b{w.e, w.v, w.pr, w.ps, w.aggpart, w.carry};
   int rc;
-#define GM_MARK(c) do { if (prof && (rc = prof->mark(c))) return rc; } while (0)
-  GM_MARK(0);
+  GM_PROF(kProfEncEdge);
   if ((rc = tc_enc_edge(m->tc_enc_edge, m->edge_dim, pos, pos_stride, conn_r, edge_attr, eref, g, b, st))) return rc;
-  GM_MARK(1);
+  GM_PROF(kProfEncNode);
   if (enc_node_done == nullptr) {
     if ((rc = tc_enc_node(m->tc_enc_node, m->tc_proc_edge[0], m->node_dim, nodes, g, b, st))) return rc;
   } else {
     GM_CUDA(cudaStreamWaitEvent(st, enc_node_done, 0));
   }
   for (int s = 0; s < m->m_steps; ++s) {
-    GM_MARK(2);
+    GM_PROF(kProfMpEdge);
     // after a join the first edge step is an ordinary launch: e then comes from the kernel right before it
     if ((rc = tc_mp_edge(m->tc_proc_edge[s], g, b, st, !(s == 0 && enc_node_done != nullptr)))) return rc;
-    GM_MARK(3);
+    GM_PROF(kProfMpNode);
     const bool last = s + 1 == m->m_steps;
     if ((rc = tc_mp_node(m->tc_proc_node[s], last ? nullptr : &m->tc_proc_edge[s + 1], last ? &m->tc_dec : nullptr,
                          m->out_dim, pred, g, b, st)))
       return rc;
   }
-  GM_MARK(-1);
-#undef GM_MARK
+  GM_PROF(-1);
   return GM_OK;
 }
 
@@ -358,11 +364,13 @@ int rollout_step(gm_rollout* r, cudaStream_t st) {
   const gm_model* m = d.model;
   const PhysParams& p = r->rp.phys;
   int rc;
+  GM_PROF(kProfControl);
   if ((rc = apply_control(d.obs, r->rp, st))) return rc;
   const float* last = d.obs + (size_t)(d.k - 1) * r->n * d.D;
   const float* pos = last + p.cart[0];
+  GM_PROF(kProfNodeFeat);
   if ((rc = node_features(d.obs, d.k, r->n, d.D, p, r->nodes, st))) return rc;
-  const bool fork = r->tc && r->side != nullptr;
+  const bool fork = r->tc && r->side != nullptr && g_profiler == nullptr;   // profiled steps run strictly serially
   if (fork) {
     // the node encoder needs the node features only: fork it onto the side stream so that it overlaps the
     // (many small) graph-build kernels; forward_tc joins before the first edge step
@@ -378,12 +386,14 @@ int rollout_step(gm_rollout* r, cudaStream_t st) {
     return rc;
   if (r->tc)
     rc = forward_tc(m, r->nodes, nullptr, pos, d.D, p.conn_r, r->n, r->max_edges, r->n_edges, r->recv_ptr, r->esend,
-                    r->erecv, r->eref, r->pred, r->fws, st, nullptr, fork ? r->ev_join : nullptr);
+                    r->erecv, r->eref, r->pred, r->fws, st, fork ? r->ev_join : nullptr);
   else
     rc = forward_simt(m, r->nodes, nullptr, pos, d.D, p.conn_r, r->n, r->max_edges, r->n_edges, r->recv_ptr,
                       r->esend, r->erecv, r->eref, r->pred, r->fws, st);
   if (rc) return rc;
+  GM_PROF(kProfIntegrate);
   if ((rc = integrate(d.obs, r->pred, r->rp, nullptr, st))) return rc;
+  GM_PROF(-1);
   if (d.pred != nullptr) {
     GM_CUDA(cudaMemcpyAsync(d.pred, r->pred, sizeof(float) * (size_t)r->n * m->out_dim, cudaMemcpyDeviceToDevice, st));
   }
@@ -652,24 +662,17 @@ int gm_model_forward_profile(const gm_model* model, const float* nodes, const fl
     set_error("gm_model_forward_profile: workspace too small (%zu < %zu bytes)", workspace_bytes, a.off);
     return GM_ERR_WORKSPACE;
   }
-  FwdProfile prof;
+  Profiler prof;
   prof.st = (cudaStream_t)stream;
+  g_profiler = &prof;
   int rc = forward_tc(model, nodes, edge_attr, pos, pos_stride, (float)conn_r, n_nodes, max_edges, n_edges_dev,
-                      recv_ptr, esend, erecv, eref, pred, w, prof.st, &prof);
-  cudaError_t ce = cudaStreamSynchronize(prof.st);
-  for (int c = 0; c < 4; ++c) { ms_host[c] = 0.f; launches_host[c] = 0; }
-  if (rc == GM_OK && ce == cudaSuccess) {
-    for (size_t i = 0; i + 1 < prof.ev.size(); ++i) {
-      float ms = 0.f;
-      cudaEventElapsedTime(&ms, prof.ev[i], prof.ev[i + 1]);
-      const int c = prof.cls[i];
-      if (c >= 0 && c < 4) { ms_host[c] += ms; launches_host[c] += 1; }
-    }
-  }
-  for (cudaEvent_t e : prof.ev) cudaEventDestroy(e);
-  if (rc) return rc;
-  if (ce != cudaSuccess) return cuda_fail(ce, "gm_model_forward_profile sync");
-  return GM_OK;
+                      recv_ptr, esend, erecv, eref, pred, w, prof.st);
+  g_profiler = nullptr;
+  float ms[kProfCount];
+  int cnt[kProfCount];
+  const int rc2 = prof.finish(ms, cnt);
+  for (int c = 0; c < 4; ++c) { ms_host[c] = ms[kProfEncEdge + c]; launches_host[c] = cnt[kProfEncEdge + c]; }
+  return rc ? rc : rc2;
 }
 
 int gm_mlp_forward(int32_t n_layers, const float* const* weights_t, const float* const* biases, const int32_t* dims,
@@ -766,7 +769,7 @@ int gm_rollout_create(gm_rollout** plan, const gm_rollout_desc* d, void* workspa
     // capture one rollout step on a private stream; replays are ordered on the caller's stream
     cudaStream_t cs;
     ce = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking);
-    if (ce != cudaSuccess) { delete r; return cuda_fail(ce, "cudaStreamCreate"); }
+    if (ce != cudaSuccess) { gm_rollout_destroy(r); return cuda_fail(ce, "cudaStreamCreate"); }
     ce = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
     if (ce == cudaSuccess) {
       const long long before = g_launch_count;
@@ -802,6 +805,17 @@ int gm_rollout_run(gm_rollout* r, int32_t steps, void* stream) {
     }
   }
   return GM_OK;
+}
+
+int gm_rollout_step_profile(gm_rollout* r, void* stream, float* ms_host, int32_t* launches_host) {
+  GM_REQUIRE(r != nullptr && ms_host != nullptr && launches_host != nullptr, "gm_rollout_step_profile: NULL argument");
+  Profiler prof;
+  prof.st = (cudaStream_t)stream;
+  g_profiler = &prof;
+  const int rc = rollout_step(r, prof.st);
+  g_profiler = nullptr;
+  const int rc2 = prof.finish(ms_host, launches_host);
+  return rc ? rc : rc2;
 }
 
 int gm_rollout_reset(gm_rollout* r, int32_t step, void* stream) {

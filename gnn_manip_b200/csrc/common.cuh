@@ -51,6 +51,39 @@ int cuda_fail(cudaError_t e, const char* what);
 
 constexpr int kNumSMs = 148;
 
+// Per-phase CUDA-event timing of one un-captured rollout step / forward (gm_rollout_step_profile,
+// gm_model_forward_profile): while a Profiler is installed on the calling thread, every launcher marks the phase it is
+// about to enqueue; the time between two marks is attributed to the first one's phase.
+enum ProfPhase : int {
+  kProfControl = 0, kProfNodeFeat, kProfGrid, kProfNeighbour, kProfCsr, kProfEncEdge, kProfEncNode, kProfMpEdge,
+  kProfMpNode, kProfIntegrate, kProfCount
+};
+struct Profiler {
+  cudaStream_t st = nullptr;
+  int n = 0;
+  static constexpr int kMax = 96;
+  cudaEvent_t ev[kMax];
+  int cls[kMax];
+  int mark(int c);             // records an event on st; c < 0 = end marker
+  int finish(float* ms_by_phase, int* launches_by_phase);   // synchronises st, accumulates, destroys the events
+};
+extern thread_local Profiler* g_profiler;
+#define GM_PROF(c) do { if (gm::g_profiler) { int _rc = gm::g_profiler->mark(c); if (_rc) return _rc; } } while (0)
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-device attribute: a "configured" flag per device (the
+// flags are atomics: two host threads may race to configure, which is harmless -- the call is idempotent).
+struct PerDeviceOnce {
+  static constexpr int kMaxDevices = 64;
+  volatile int done[kMaxDevices] = {};
+  // returns the current device index if it still needs configuring, -1 if already done, -2 on error
+  int begin() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return -2;
+    return done[dev] ? -1 : dev;
+  }
+  void finish(int dev) { done[dev] = 1; }
+};
+
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 

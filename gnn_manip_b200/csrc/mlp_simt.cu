@@ -145,13 +145,14 @@ __global__ void gather_rows_kernel(const float* __restrict__ src, int F, const i
 
 }  // namespace
 
-// opt in to > 48 KB dynamic shared memory once per process (not legal inside a stream capture)
+// opt in to > 48 KB dynamic shared memory once per device (not legal inside a stream capture)
 int mlp_simt_configure() {
-  static bool done = false;
-  if (!done) {
-    GM_CUDA(cudaFuncSetAttribute(mlp_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)));
-    done = true;
-  }
+  static PerDeviceOnce once;
+  const int dev = once.begin();
+  if (dev == -1) return GM_OK;
+  GM_REQUIRE(dev >= 0, "mlp_simt_configure: cannot query the current device");
+  GM_CUDA(cudaFuncSetAttribute(mlp_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)));
+  once.finish(dev);
   return GM_OK;
 }
 

@@ -384,8 +384,6 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(half ? bar_a1 : bar_a0);
     };
-    auto poll_half0 = [&]() {};
-    auto issue_gemm = [&]() {};
     auto publish_both = [&]() {
       tmem_st_wait();
       tc_fence_before();
@@ -445,10 +443,7 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
 #pragma unroll
       for (int i = 0; i < 4; ++i) prefetch_l1(pr_row + 32 * i);
       stage_rows32_gather(db, b.ps + 4 * lane, cur_send);
-      if (issue) {                               // (inside the loop GEMM 1 was already issued under LayerNorm)
-        publish_both();
-        issue_gemm();
-      }
+      if (issue) publish_both();                 // (inside the loop GEMM 1 was already issued under LayerNorm)
     };
     if (K0 < n_my) {
       fetch_ids(K0);
@@ -460,7 +455,7 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
     if (K0 < n_my) {
       operand_from_stage();
       publish_both();                            // layer 1 of the first tile needs e and weights only: its GEMM runs
-      issue_gemm();                              // before the dependency wait as well
+                                                 // before the dependency wait as well
     }
     // Everything so far read only constants and e, which the kernel two launches back (the previous edge kernel /
     // the edge encoder) finished writing before this grid could start; Pr / Ps come from the node kernel right before.
@@ -528,7 +523,6 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
         tmem_ld_wait();
         tmem_ld32(tY + 96, vb);
         e1_block(2, va, pa);
-        poll_half0();
         GM_ESTAMP(19);
         tmem_ld_wait();
         e1_block(3, vb, pb);
@@ -539,7 +533,6 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
       // the staging rows are free until the LayerNorm rows go in: the e rows of this slot's next tile land here
       // while layers 2 and 3 run (issued before the issuer blocks on the other warps' hand-off)
       if (has_next) stage_e_rows(k + KSTEP);
-      issue_gemm();
       GM_ESTAMP(22);
       GM_ESTAMP(6);
       // ---- layer 2 epilogue: relu(D + b2) ----
@@ -573,12 +566,10 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
         tmem_ld_wait();
         tmem_ld32(tX + 96, vb);
         e2_block(2, va);
-        poll_half0();
         tmem_ld_wait();
         e2_block(3, vb);
       }
       publish_half(1);
-      issue_gemm();
       GM_ESTAMP(8);
       // ---- layer 3 epilogue: y = LayerNorm(D + b3) -> staging row ----
       mbar_wait(bar_d, ph_d);
@@ -641,7 +632,6 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
         }
       }
       __syncwarp();
-      if (has_next) issue_gemm();                  // by now every warp of the pair has published: no stall for the issuer
       GM_ESTAMP(10);
       // ---- e' = e + y (epd_gnn.py:104): this warp's rows leave as 512 B vector reductions, the add happens in L2 ----
       {
@@ -753,7 +743,8 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
 // No cross-warp hand-off exists inside a CTA besides the MMA barriers.
 // ================================================================================================
 __global__ void __launch_bounds__(kNTE, 1)
-enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, float conn_r, TcGraph g, TcBuffers b) {
+enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, float conn_r,
+                     const float* __restrict__ edge_attr, const int* __restrict__ eref, TcGraph g, TcBuffers b) {
   extern __shared__ __align__(1024) char smem_raw[];
   char* base = smem_raw;
   const uint32_t W_s = smem_u32(base);
@@ -824,8 +815,10 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
   };
   auto load_x = [&](int k) -> float4 {
     const int ge = (blockIdx.x + k * grid) * kTile + r;
-    if (ge < E) return edge_feature(pos, pos_stride, __ldg(g.esend + ge), __ldg(g.erecv + ge), conn_r);
-    return make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ge >= E) return make_float4(0.f, 0.f, 0.f, 0.f);
+    if (edge_attr != nullptr)      // explicit [E, 4] features in the caller's edge order (eref: receiver-major -> caller's id)
+      return __ldg(reinterpret_cast<const float4*>(edge_attr) + (eref ? __ldg(eref + ge) : ge));
+    return edge_feature(pos, pos_stride, __ldg(g.esend + ge), __ldg(g.erecv + ge), conn_r);
   };
   // layer 1 on CUDA cores: relu(W1 x + b1) -> bf16 hi / lo operand in TMEM (same FMA order as the SIMT path)
   auto layer1 = [&](const float4& x) {
@@ -1038,12 +1031,14 @@ int tc_debug_stamps_edge(unsigned long long* out_host, int n) {
 }
 
 int tc_configure_edge() {
-  static bool done = false;
-  if (done) return GM_OK;
+  static PerDeviceOnce once;
+  const int dev = once.begin();
+  if (dev == -1) return GM_OK;
+  GM_REQUIRE(dev >= 0, "tc_configure_edge: cannot query the current device");
   GM_CUDA(cudaFuncSetAttribute(mp_edge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEdgeSmemBytes));
   GM_CUDA(cudaFuncSetAttribute(enc_edge_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEdgeSmemBytes));
   GM_CUDA(cudaFuncSetAttribute(selftest_gemm_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSelftestTsSmem));
-  done = true;
+  once.finish(dev);
   return GM_OK;
 }
 
@@ -1061,15 +1056,15 @@ int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_
   return GM_OK;
 }
 
-// on-the-fly edge features (edge_dim == 4): the CTA-pair pipeline
-int tc_enc_edge_pair(const TcMlp& m, const float* pos, int pos_stride, float conn_r, const TcGraph& g,
-                     const TcBuffers& b, cudaStream_t stream) {
+// edge_dim == 4 (on-the-fly displacement features from positions, or an explicit [E, 4] edge_attr): the CTA-pair pipeline
+int tc_enc_edge_pair(const TcMlp& m, const float* pos, int pos_stride, float conn_r, const float* edge_attr,
+                     const int* eref, const TcGraph& g, const TcBuffers& b, cudaStream_t stream) {
   if (g.max_edges <= 0) return GM_OK;
   int rc = tc_configure_edge();
   if (rc) return rc;
   const int grid = min((ceil_div(g.max_edges, kTile) + 1) & ~1, kNumSMs & ~1);
   GM_CUDA(launch_pdl(enc_edge_pair_kernel, grid, kNTE, (size_t)kEdgeSmemBytes, stream, 2, m, pos, pos_stride, conn_r,
-                     g, b));
+                     edge_attr, eref, g, b));
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("enc_edge_pair_kernel");
   return GM_OK;

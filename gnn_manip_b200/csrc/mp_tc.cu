@@ -826,16 +826,18 @@ int set_smem(Kern kern, size_t bytes) {
 
 }  // namespace
 
-// opt in to the large dynamic shared-memory carve-outs once per process (outside any stream capture)
+// opt in to the large dynamic shared-memory carve-outs once per device (outside any stream capture)
 int tc_configure() {
-  static bool done = false;
-  if (done) return GM_OK;
+  static PerDeviceOnce once;
+  const int dev = once.begin();
+  if (dev == -1) return GM_OK;
+  GM_REQUIRE(dev >= 0, "tc_configure: cannot query the current device");
   int rc;
   if ((rc = set_smem(mp_node_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(enc_node_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(enc_edge_kernel, smem_bytes(2)))) return rc;
   if ((rc = set_smem(selftest_gemm_kernel, smem_bytes(1)))) return rc;
-  done = true;
+  once.finish(dev);
   return GM_OK;
 }
 
@@ -883,7 +885,10 @@ int tc_enc_edge(const TcMlp& m, int edge_dim, const float* pos, int pos_stride, 
   GM_REQUIRE(edge_dim >= 1 && edge_dim <= kMaxIn1, "tc_enc_edge: edge_dim=%d outside [1,%d]", edge_dim, kMaxIn1);
   GM_REQUIRE(edge_attr != nullptr || edge_dim == 4, "tc_enc_edge: on-the-fly edge features need edge_dim == 4");
   if (g.max_edges <= 0) return GM_OK;
-  if (edge_attr == nullptr) return tc_enc_edge_pair(m, pos, pos_stride, conn_r, g, b, stream);
+  // edge_dim == 4 (the reference's displacement features): the CTA-pair pipeline, features on the fly or explicit;
+  // the single-CTA kernel below only serves other edge widths of the block API
+  if (edge_attr == nullptr || (edge_dim == 4 && ((uintptr_t)edge_attr & 15) == 0))
+    return tc_enc_edge_pair(m, pos, pos_stride, conn_r, edge_attr, eref, g, b, stream);
   const size_t sm = smem_bytes(2);
   int rc = tc_configure();
   if (rc) return rc;

@@ -51,8 +51,8 @@ int tc_enc_edge(const TcMlp& m, int edge_dim, const float* pos, int pos_stride, 
                 const float* edge_attr /*optional explicit [E,edge_dim] in receiver-major order*/,
                 const int* eref /*optional: row map into edge_attr*/, const TcGraph& g, const TcBuffers& b,
                 cudaStream_t stream);
-int tc_enc_edge_pair(const TcMlp& m, const float* pos, int pos_stride, float conn_r, const TcGraph& g,
-                     const TcBuffers& b, cudaStream_t stream);
+int tc_enc_edge_pair(const TcMlp& m, const float* pos, int pos_stride, float conn_r, const float* edge_attr,
+                     const int* eref, const TcGraph& g, const TcBuffers& b, cudaStream_t stream);
 int tc_enc_node(const TcMlp& m, const TcMlp& next_edge, int node_dim, const float* nodes, const TcGraph& g,
                 const TcBuffers& b, cudaStream_t stream);
 int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_t stream, bool programmatic = true);

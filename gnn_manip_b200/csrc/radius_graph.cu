@@ -366,58 +366,6 @@ __global__ void recv_fill_kernel(const int* __restrict__ recv_of_slot, long long
   keys[at] = (int)s;
 }
 
-// One thread per receiver: sort its slot keys ascending (== ascending sender, == reference edge order),
-// then emit sender / receiver / reference edge id for every sorted edge.
-__global__ void recv_sort_emit_kernel(const int* __restrict__ recv_ptr, int n, int* __restrict__ keys,
-                                      int K /*>0: slot = sender*K + s; 0: slot = edge id*/,
-                                      const int* __restrict__ edge_ptr, const int* __restrict__ send_of_slot,
-                                      int* __restrict__ esend, int* __restrict__ erecv, int* __restrict__ eref) {
-  int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n) return;
-  const int b = recv_ptr[j], e = recv_ptr[j + 1];
-  const int len = e - b;
-  constexpr int kLocal = 48;
-  if (len <= kLocal) {
-    int buf[kLocal];
-#pragma unroll 1
-    for (int t = 0; t < len; ++t) buf[t] = keys[b + t];
-#pragma unroll 1
-    for (int t = 1; t < len; ++t) {
-      int v = buf[t], u = t - 1;
-      while (u >= 0 && buf[u] > v) {
-        buf[u + 1] = buf[u];
-        --u;
-      }
-      buf[u + 1] = v;
-    }
-#pragma unroll 1
-    for (int t = 0; t < len; ++t) keys[b + t] = buf[t];
-  } else {
-    for (int t = b + 1; t < e; ++t) {
-      int v = keys[t], u = t - 1;
-      while (u >= b && keys[u] > v) {
-        keys[u + 1] = keys[u];
-        --u;
-      }
-      keys[u + 1] = v;
-    }
-  }
-  for (int t = b; t < e; ++t) {
-    const int slot = keys[t];
-    int snd, ref;
-    if (K > 0) {
-      snd = slot / K;
-      ref = edge_ptr[snd] + (slot - snd * K);
-    } else {
-      snd = send_of_slot[slot];
-      ref = slot;
-    }
-    esend[t] = snd;
-    erecv[t] = j;
-    eref[t] = ref;
-  }
-}
-
 // Warp per receiver: every lane ranks its one or two keys against the whole segment with shuffles and
 // writes the sorted edge straight out (keys are distinct slot ids, so ranks are a permutation).
 __global__ void __launch_bounds__(256)
@@ -550,6 +498,7 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
   GridParams* gp = reinterpret_cast<GridParams*>(ws.grid);
 
   const bool small = n <= kSmallN;
+  GM_PROF(kProfGrid);
   if (small) {
     GM_CUDA(launch_pdl(prepare_small_kernel, 1, 1024, 0, stream, 1, pos, pos_stride, n, r, n_graphs, ws.max_cells, gp, ws.cell_cnt,
                        ws.indeg));
@@ -570,10 +519,12 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
   if (rc) return rc;
   GM_CUDA(launch_pdl(cell_fill_kernel, ceil_div(n, T), T, 0, stream, 1, pos, pos_stride, n, ws.cell_of, ws.cell_start,
                      ws.cell_cnt, ws.sorted));
+  GM_PROF(kProfNeighbour);
   GM_CUDA(launch_pdl(neighbour_kernel, ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream, 1, ws.sorted, ws.cell_start, gp, n,
                      n_per_graph, r * r, K, nbr, cnt, ws.indeg));
   GM_LAUNCHED(3);
   GM_LAUNCH_CHECK("radius_graph kernels");
+  GM_PROF(kProfCsr);
   rc = exclusive_scan_i32(cnt, edge_ptr, n, ws.scan_ws, stream, n_edges);
   if (rc) return rc;
   return build_recv_csr(nbr, (long long)n * K, nullptr, n, K, edge_ptr, nullptr, ws.indeg, ws.fill, ws.keys,

@@ -43,7 +43,13 @@ def mlp_forward(phi, sources, indices, n_rows):
     f32 = dict(device=dev, dtype=torch.float32)
     srcs = [s.detach().to(**f32).contiguous() for s in sources]
     idxs = [None if i is None else i.detach().to(device=dev, dtype=torch.int32).contiguous() for i in indices]
-    wts = [l.weight.detach().to(**f32).t().contiguous() for l in linears]
+    # transposed weights are cached on the Sequential per (device, parameter versions)
+    wkey = (str(dev),) + tuple((l.weight.data_ptr(), l.weight._version) for l in linears)
+    hit = getattr(phi, "_gm_wt_cache", None)
+    if hit is None or hit[0] != wkey:
+        hit = (wkey, [l.weight.detach().to(**f32).t().contiguous() for l in linears])
+        phi._gm_wt_cache = hit
+    wts = hit[1]
     bs = [None if l.bias is None else l.bias.detach().to(**f32).contiguous() for l in linears]
     dims = [linears[0].in_features] + [l.out_features for l in linears]
     g = None if ln is None else ln.weight.detach().to(**f32).contiguous()

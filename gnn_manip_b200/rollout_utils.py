@@ -124,9 +124,9 @@ class Rollout:
             check(_lib.lib().gm_rollout_run(self.handle, int(steps), stream_ptr(self.device)), "gm_rollout_run")
         return self.obs
 
-    def graph(self):
-        """(nbr [n,K], cnt [n], edge_ptr [n+1], n_edges [1], nodes [n,F]) of the most recent step, as tensors
-        copied out of the plan's workspace."""
+    def graph_handles(self):
+        """Live views into the plan's workspace: (nbr [n,K], cnt [n], edge_ptr [n+1], n_edges [1], nodes [n,F]) of the
+        most recent step (overwritten by the next one)."""
         L = _lib.lib()
         p = [ctypes.c_void_p() for _ in range(5)]
         check(L.gm_rollout_graph(self.handle, *[ctypes.byref(x) for x in p]), "gm_rollout_graph")
@@ -135,10 +135,14 @@ class Rollout:
 
         def view(pv, count, dtype):
             off = pv.value - base
-            return self.workspace[off: off + count * 4].view(dtype).clone()
+            return self.workspace[off: off + count * 4].view(dtype)
         return (view(p[0], n * K, torch.int32).reshape(n, K), view(p[1], n, torch.int32),
                 view(p[2], n + 1, torch.int32), view(p[3], 1, torch.int32),
                 view(p[4], n * F, torch.float32).reshape(n, F))
+
+    def graph(self):
+        """Copies of graph_handles()."""
+        return tuple(t.clone() for t in self.graph_handles())
 
     def close(self):
         if getattr(self, "handle", None):
@@ -152,11 +156,63 @@ class Rollout:
             pass
 
 
-def compute_rollout(model, graph_attr, state, trajectory, steps, **kw):
-    """Stand-alone rollout (rollout_utils.py:14-67 with a control trajectory): returns the final observation
-    window [k, N, D] on the device of the input state."""
+def rollout_final_state(model, graph_attr, state, trajectory, steps, **kw):
+    """Device-resident rollout of `steps` steps from `state` under a rigid-body trajectory [T, n_rigid, 3]: the final
+    observation window [k, N, D] on the device of the input state (the end state cma_objective scores)."""
     obs = state[0] if isinstance(state, (tuple, list)) else state
     plan = Rollout(model, graph_attr, obs, trajectory=trajectory, **kw)
     out = plan.run(steps).to(obs.device).clone()
     plan.close()
     return out
+
+
+def perform_prediction(dataset, model, current_state, device=None):
+    """gnn_manip/utils/rollout_utils.py:95-107: one prediction through the reference-shaped calls (graph + features,
+    model forward, Euler step) -- every one of them a CUDA kernel sequence behind the C ABI."""
+    batch = dataset.graph_attr.process_collate([current_state])
+    pred_acc = model.forward(batch[0], batch[1], batch[2])
+    return get_position_from_prediction(dataset.stats, dataset.cartesian_idx, pred_acc, current_state[0])
+
+
+def compute_rollout(dataset, model, args):
+    """gnn_manip/utils/rollout_utils.py:14-67, same contract: returns prediction [T, N, D] (numpy float64), row i = the
+    last frame of the state after the rigid control of step i was written and before the model moved it.
+
+    args.cma_traj (path of a saved [T, 2] (rotation [rad], translation) array, :24-31): the whole loop runs as one
+    device-resident plan (CUDA-graph replay per step); only the recorded frames come back.  Without it the rigid
+    particles follow the dataset's ground truth (:33, 45, 60) through the per-step reference-shaped calls.
+    Unlike the reference, dataset[0]'s stored tensor is NOT mutated (the reference advances it in place, :37, 47-54)."""
+    k_steps = getattr(args, "k_steps", dataset.k)
+    cma_traj = getattr(args, "cma_traj", None)
+    nof_steps = dataset.time_steps if cma_traj is not None else dataset.time_steps - k_steps
+    obs0 = dataset[0][0]
+    nof_particles, data_dim = obs0.shape[1], obs0.shape[2]
+    rigid = obs0[0, :, dataset.material_id] == 1
+    prediction = np.zeros((nof_steps, nof_particles, data_dim))
+    if cma_traj is not None:
+        actions = np.load(cma_traj) if isinstance(cma_traj, str) else np.asarray(cma_traj)
+        ty_init = getattr(args, "ty_init", (0.5, 0.5, 0.4))
+        plan = Rollout(model, dataset.graph_attr, obs0, rot=actions[:nof_steps, 0], ty=actions[:nof_steps, 1],
+                       ty_init=tuple(ty_init), use_cuda_graph=True,
+                       device=getattr(args, "device", None) if str(getattr(args, "device", "cpu")) != "cpu" else None)
+        frames = torch.empty((nof_steps, nof_particles, data_dim), dtype=torch.float32, device=plan.device)
+        for i in range(nof_steps):
+            plan.run(1)
+            frames[i].copy_(plan.obs[-2], non_blocking=True)     # the pre-shift last frame, control columns included
+        prediction[:] = frames.cpu().numpy()
+        plan.close()
+        return prediction
+    groundtruth = torch.stack([dataset[i][0][-1] for i in range(nof_steps)]).float()
+    current = (obs0.clone(), dataset[0][1].clone())
+    cart, ctrl = dataset.cartesian_idx, dataset.control_idx
+    for i in range(nof_steps):
+        new_rigid = current[0][-1, rigid, :].clone()
+        new_rigid[:, ctrl] = groundtruth[i, rigid, :][:, ctrl]
+        current[0][-1, rigid, :] = new_rigid
+        prediction[i] = current[0][-1].numpy()
+        next_pos = perform_prediction(dataset, model, current)
+        current[0][:-1] = current[0][1:].clone()
+        current[0][-1][:, cart] = next_pos.detach().clone()
+        new_rigid[:, cart] = groundtruth[i, rigid, :][:, cart]
+        current[0][-1, rigid, :] = new_rigid.clone()
+    return prediction

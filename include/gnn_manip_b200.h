@@ -197,6 +197,11 @@ int gm_rollout_create(gm_rollout** plan, const gm_rollout_desc* desc_host, void*
  * still ordered by `stream` from the caller's point of view. */
 int gm_rollout_run(gm_rollout* plan, int32_t steps, void* stream);
 int gm_rollout_reset(gm_rollout* plan, int32_t step, void* stream);
+/* Measurement aid: run ONE rollout step un-captured and strictly serially on `stream` with a CUDA event between
+ * phases; synchronises the stream.  ms_host / launches_host [10]: apply_control, node_features, cell grid build,
+ * neighbour_kernel, edge_ptr scan + receiver CSR sort, enc_edge, enc_node, mp_edge (all steps), mp_node (all steps),
+ * integrate.  The step advances the plan's state like gm_rollout_run(plan, 1). */
+int gm_rollout_step_profile(gm_rollout* plan, void* stream, float* ms_host, int32_t* launches_host);
 /* device pointers into the plan's workspace holding the graph of the most recent step (for parity tests) */
 int gm_rollout_graph(const gm_rollout* plan, const int32_t** nbr, const int32_t** cnt, const int32_t** edge_ptr,
                      const int32_t** n_edges, const float** nodes);

@@ -156,10 +156,26 @@ def golden_rollout_c2(ref, horizon=300, marks=(10, 50, 150, 300)):
     with contextlib.redirect_stdout(io.StringIO()):
         solver = Solver(Recorder(), ga, (obs.clone(), nxt.clone()), scene.RX_INIT_DEG, scene.TY_INIT, 0.05, 1.0,
                         1.0, 1.0, 1.0, 1.0, 1.0, "cpu", total_steps=horizon, traj_points=1)
-    solver.cma_objective(np.zeros(2))
+    # full state windows entering steps 0 / 100 / 200 / 294 (control columns of that step already written): start
+    # states of the CPU-baseline samples in bench.py, so that the timed CPU steps cover the horizon the GPU rolls out
+    starts, windows, step_no = (0, 100, 200, 294), {}, [0]
+    orig = ref.traj.get_position_from_prediction
+
+    def spy(stats, cart, pred, window):
+        if step_no[0] in starts:
+            windows[step_no[0]] = window.clone().numpy()
+        step_no[0] += 1
+        return orig(stats, cart, pred, window)
+
+    ref.traj.get_position_from_prediction = spy
+    try:
+        solver.cma_objective(np.zeros(2))
+    finally:
+        ref.traj.get_position_from_prediction = orig
     np.savez_compressed(os.path.join(GOLDEN_DIR, "rollout_c2.npz"), horizon=horizon, marks=np.array(marks),
                         n_rigid=n_rigid, rot=rot, ty=ty, n_edges=np.array(n_edges, dtype=np.int32),
-                        weights_seed=0, **{f"sand_{t}": out[t] for t in marks})
+                        weights_seed=0, starts=np.array(starts), **{f"sand_{t}": out[t] for t in marks},
+                        **{f"obs_{t}": windows[t] for t in starts})
     print("rollout_c2: edges per step first/mean/last", n_edges[0], float(np.mean(n_edges)), n_edges[-1])
 
 
