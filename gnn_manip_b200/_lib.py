@@ -10,7 +10,8 @@ from ctypes import POINTER, c_char_p, c_double, c_float, c_int32, c_int64, c_lon
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgnn_manip_b200.so")
+# GNN_MANIP_B200_LIB selects a debug variant of the library (csrc/Makefile VARIANT=...), e.g. the phase-stamp build
+LIB_PATH = os.environ.get("GNN_MANIP_B200_LIB") or os.path.join(_HERE, "libgnn_manip_b200.so")
 
 GM_IMPL_AUTO, GM_IMPL_SIMT, GM_IMPL_TC = 0, 1, 2
 

@@ -8,7 +8,7 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 100_000
 torch.manual_seed(0)
 model = gm.EncProcDecGNN(25, 4, 3, 128, 2, 10)
 obs, _ = scenes.make_state(n, seed=0, n_rigid=0)
-per, E, N = bench.profile_forward(gm, model, obs, reps=2, warm=1, flush=None)
+per, E, N, _ = bench.profile_forward(gm, model, obs, reps=2, warm=1, flush=None)
 st = (ctypes.c_ulonglong * 64)()
 gm._lib.check(gm._lib.lib().gm_debug_stamps(st, 64), "gm_debug_stamps")
 s = np.array(st[:], dtype=np.int64)
