@@ -53,6 +53,10 @@ class gm_traj_param(ctypes.Structure):
 
 GM_TRAJ_INCREMENTS, GM_TRAJ_PCHIP = 0, 1
 
+
+class gm_pack_job(ctypes.Structure):
+    _fields_ = [("w", c_void_p), ("ld", c_int32), ("col0", c_int32), ("transpose", c_int32), ("chunk", c_void_p)]
+
 # name -> (restype, argtypes); every symbol of include/gnn_manip_b200.h
 SIGNATURES = {
     "gm_version": (ctypes.c_int, []),
@@ -101,6 +105,23 @@ SIGNATURES = {
     "gm_sinkhorn_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32]),
     "gm_sinkhorn_divergence": (ctypes.c_int, [c_void_p, c_int32, c_int64, c_void_p, c_int32, c_void_p, c_int32, c_int32,
                                               c_double, c_double, c_double, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "gm_train_pack": (ctypes.c_int, [c_void_p, c_int32, c_void_p]),
+    "gm_train_gemm": (ctypes.c_int, [c_void_p] * 9 + [c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p]),
+    "gm_train_wgrad_partial_bytes": (c_size_t, []),
+    "gm_train_wgrad": (ctypes.c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_void_p,
+                                      c_void_p, c_void_p]),
+    "gm_train_layernorm_fwd": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_int32] + [c_void_p] * 6),
+    "gm_train_layernorm_partial_bytes": (c_size_t, [c_int32]),
+    "gm_train_layernorm_bwd": (ctypes.c_int, [c_void_p] * 6 + [c_int32] + [c_void_p] * 5),
+    "gm_train_small_fwd": (ctypes.c_int, [c_void_p, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p,
+                                          c_void_p]),
+    "gm_train_small_partial_bytes": (c_size_t, [c_int32, c_int32, c_int32]),
+    "gm_train_small_bwd": (ctypes.c_int, [c_void_p, c_int32, c_void_p, c_int32, c_void_p, c_void_p, c_int32] +
+                           [c_void_p] * 5),
+    "gm_train_l1_loss": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_void_p,
+                                        c_void_p]),
+    "gm_adam_step": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float,
+                                    c_float, c_int32, c_void_p]),
     "gm_debug_stamps": (ctypes.c_int, [c_void_p, c_int32]),
     "gm_selftest_gemm": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),
     "gm_selftest_gemm_ts": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),

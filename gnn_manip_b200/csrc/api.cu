@@ -12,6 +12,7 @@
 #include "physics.cuh"
 #include "radius_graph.cuh"
 #include "scan.cuh"
+#include "train.cuh"
 #include "sinkhorn.cuh"
 #include "traj.cuh"
 
@@ -891,6 +892,64 @@ int gm_sinkhorn_divergence(const float* x, int32_t x_stride, int64_t x_batch_str
   if (iters > kSinkMaxEps) iters = kSinkMaxEps;
   return sinkhorn_divergence(x, x_stride, x_batch_stride, x_idx, n, y, m, n_batch, blur, scaling, iters, loss, ws,
                              (cudaStream_t)stream);
+}
+
+static_assert(sizeof(gm_pack_job) == sizeof(TrPackJob), "gm_pack_job and TrPackJob must have the same layout");
+
+int gm_train_pack(const gm_pack_job* jobs_dev, int32_t n_jobs, void* stream) {
+  return tr_pack(reinterpret_cast<const TrPackJob*>(jobs_dev), n_jobs, (cudaStream_t)stream);
+}
+
+int gm_train_gemm(const float* x, const int32_t* in_idx, const void* chunk, const float* bias, const float* add1,
+                  const int32_t* idx1, const float* add2, const int32_t* idx2, const float* mask, int32_t relu,
+                  int32_t accumulate, int32_t n_rows, const int32_t* n_rows_dev, float* out, void* stream) {
+  TrGemmArgs a{x, in_idx, chunk, bias, add1, idx1, add2, idx2, mask, out, relu, accumulate, n_rows, n_rows_dev};
+  return tr_gemm(a, (cudaStream_t)stream);
+}
+
+size_t gm_train_wgrad_partial_bytes(void) { return tr_wgrad_partial_floats() * sizeof(float); }
+
+int gm_train_wgrad(const float* A, const float* B, int32_t n_rows, const int32_t* n_rows_dev, float* dW, int32_t ld,
+                   int32_t col0, float* dbias, void* partial, void* stream) {
+  return tr_wgrad(A, B, n_rows, n_rows_dev, dW, ld, col0, dbias, (float*)partial, (cudaStream_t)stream);
+}
+
+int gm_train_layernorm_fwd(const float* z, const float* gamma, const float* beta, int32_t n_rows, float* xhat,
+                           float* rstd, float* y, const float* res_in, float* res_out, void* stream) {
+  return tr_ln_fwd(z, gamma, beta, n_rows, nullptr, xhat, rstd, y, res_in, res_out, (cudaStream_t)stream);
+}
+
+size_t gm_train_layernorm_partial_bytes(int32_t n_rows) { return tr_ln_partial_floats(n_rows) * sizeof(float); }
+
+int gm_train_layernorm_bwd(const float* d1, const float* d2, const int32_t* idx2, const float* xhat, const float* rstd,
+                           const float* gamma, int32_t n_rows, float* dz, float* dgamma, float* dbeta, void* partial,
+                           void* stream) {
+  return tr_ln_bwd(d1, d2, idx2, xhat, rstd, gamma, n_rows, nullptr, dz, dgamma, dbeta, (float*)partial,
+                   (cudaStream_t)stream);
+}
+
+int gm_train_small_fwd(const float* x, int32_t K, const float* w, const float* b, int32_t O, int32_t n_rows,
+                       int32_t relu, float* h, void* stream) {
+  return tr_small_fwd(x, K, w, b, O, n_rows, nullptr, relu, h, (cudaStream_t)stream);
+}
+
+size_t gm_train_small_partial_bytes(int32_t n_rows, int32_t K, int32_t O) {
+  return tr_small_partial_floats(n_rows, K, O) * sizeof(float);
+}
+
+int gm_train_small_bwd(const float* x, int32_t K, const float* w, int32_t O, const float* dh, const float* mask,
+                       int32_t n_rows, float* dW, float* db, float* dx, void* partial, void* stream) {
+  return tr_small_bwd(x, K, w, O, dh, mask, n_rows, nullptr, dW, db, dx, (float*)partial, (cudaStream_t)stream);
+}
+
+int gm_train_l1_loss(const float* pred, const float* tgt, const uint8_t* row_mask, int32_t n_rows, int32_t width,
+                     float* loss, float* dpred, float* scratch, void* stream) {
+  return tr_l1_loss(pred, tgt, row_mask, n_rows, width, loss, dpred, scratch, (cudaStream_t)stream);
+}
+
+int gm_adam_step(float* params, const float* grads, float* m, float* v, size_t n, float lr, float beta1, float beta2,
+                 float eps, int32_t step, void* stream) {
+  return tr_adam(params, grads, m, v, n, lr, beta1, beta2, eps, step, (cudaStream_t)stream);
 }
 
 #ifdef GM_TRACE

@@ -258,6 +258,45 @@ int gm_sinkhorn_divergence(const float* x, int32_t x_stride, int64_t x_batch_str
                            const float* y, int32_t m, int32_t n_batch, double blur, double scaling,
                            double diameter_max, float* loss, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- Rows E(2) + N3: training step building blocks (examples/train_dyn.py:49-72) -------------------------------
+ * Every 128-wide Linear of forward, dgrad and wgrad is a tcgen05 GEMM (bf16x3 operand split, fp32 accumulation);
+ * activations are fp32 [rows, 128].  gm_train_* below are the kernels gm_train_step is built from, exported so that
+ * each one is parity-tested on its own (tests/test_gpu_train.py). */
+/* pack n_jobs 128 x 128 blocks into 64 KB operand chunks; jobs_dev: device array of gm_pack_job */
+typedef struct gm_pack_job {
+  const float* w;       /* [128 rows][ld] fp32, device */
+  int32_t ld, col0;     /* columns [col0, col0 + 128) */
+  int32_t transpose;    /* 0: B = w (y = x w^T, forward);  1: B = w^T (dx = dy w, dgrad) */
+  void* chunk;          /* 64 KB, 1024-byte aligned, device */
+} gm_pack_job;
+int gm_train_pack(const gm_pack_job* jobs_dev, int32_t n_jobs, void* stream);
+/* out[r] (+)= mask o relu?( x[in_idx[r]] @ B^T + bias + add1[idx1[r]] + add2[idx2[r]] ); every optional pointer may be NULL */
+int gm_train_gemm(const float* x, const int32_t* in_idx, const void* chunk, const float* bias, const float* add1,
+                  const int32_t* idx1, const float* add2, const int32_t* idx2, const float* mask, int32_t relu,
+                  int32_t accumulate, int32_t n_rows, const int32_t* n_rows_dev, float* out, void* stream);
+/* dW[128, ld][:, col0:col0+128] += A^T B, dbias (optional) += column sums of A; partial: gm_train_wgrad_partial_bytes() */
+size_t gm_train_wgrad_partial_bytes(void);
+int gm_train_wgrad(const float* A, const float* B, int32_t n_rows, const int32_t* n_rows_dev, float* dW, int32_t ld,
+                   int32_t col0, float* dbias, void* partial, void* stream);
+int gm_train_layernorm_fwd(const float* z, const float* gamma, const float* beta, int32_t n_rows, float* xhat,
+                           float* rstd, float* y, const float* res_in, float* res_out, void* stream);
+size_t gm_train_layernorm_partial_bytes(int32_t n_rows);
+int gm_train_layernorm_bwd(const float* d1, const float* d2, const int32_t* idx2, const float* xhat, const float* rstd,
+                           const float* gamma, int32_t n_rows, float* dz, float* dgamma, float* dbeta, void* partial,
+                           void* stream);
+int gm_train_small_fwd(const float* x, int32_t K, const float* w, const float* b, int32_t O, int32_t n_rows,
+                       int32_t relu, float* h, void* stream);
+size_t gm_train_small_partial_bytes(int32_t n_rows, int32_t K, int32_t O);
+int gm_train_small_bwd(const float* x, int32_t K, const float* w, int32_t O, const float* dh, const float* mask,
+                       int32_t n_rows, float* dW, float* db, float* dx, void* partial, void* stream);
+/* L1Loss(reduction='sum') / n_selected_rows (train_dyn.py:56-64, 109); row_mask (bytes, optional) selects rows;
+ * scratch: 2 + 2 * ceil(n_rows / 256) floats */
+int gm_train_l1_loss(const float* pred, const float* tgt, const uint8_t* row_mask, int32_t n_rows, int32_t width,
+                     float* loss, float* dpred, float* scratch, void* stream);
+/* torch.optim.Adam step t = 1, 2, ... on a flat vector (train_dyn.py:98: Adam(lr), default betas / eps) */
+int gm_adam_step(float* params, const float* grads, float* m, float* v, size_t n, float lr, float beta1, float beta2,
+                 float eps, int32_t step, void* stream);
+
 /* Debug aid: phase timestamps (clock64) recorded by CTA 0 of the instrumented kernels; only in -DGM_STAMPS builds
  * (returns GM_STATUS_UNSUPPORTED otherwise).  out_host: host array of n <= 64 values. */
 int gm_debug_stamps(unsigned long long* out_host, int32_t n);
