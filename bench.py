@@ -580,11 +580,11 @@ if __name__ == "__main__":
     _real_stdout = os.dup(1)
     os.dup2(2, 1)
     sys.stdout = os.fdopen(_real_stdout, "w")
-    if a.impl == "reference":
-        run_reference(a)
-    elif a.workload == "c5":
+    if a.workload == "c5":
         import bench_train
         bench_train.run(a)
+    elif a.impl == "reference":
+        run_reference(a)
     else:
         run_ours(a)
     sys.stdout.flush()

@@ -17,7 +17,8 @@ from .rollout_utils import (Rollout, compute_rollout, get_position_from_predicti
 from .coffee_dataset import CoffeeDataset, CoffeeTestDataset, read_metadata, save_as_csv  # noqa: F401
 from .traj_utils import (CMAESolver, InterpolatedCMAsolver, TrajectoryCMAsolver,  # noqa: F401
                          sinkhorn_divergence)
+from .train_dyn import Batch, Trainer, average_gradients, make_batch  # noqa: F401
 from .utils import (compute_acceleration, get_connectivity, get_edges_displacement,  # noqa: F401
-                    get_nodes_vel, radius_graph)
+                    get_nodes_vel, radius_graph, random_walk_noise)
 
 __version__ = "0.1.0"

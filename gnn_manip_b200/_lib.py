@@ -54,6 +54,15 @@ class gm_traj_param(ctypes.Structure):
 GM_TRAJ_INCREMENTS, GM_TRAJ_PCHIP = 0, 1
 
 
+class gm_train_desc(ctypes.Structure):
+    _fields_ = [("node_dim", c_int32), ("edge_dim", c_int32), ("out_dim", c_int32), ("hidden", c_int32),
+                ("num_layers", c_int32), ("m_steps", c_int32), ("max_nodes", c_int32), ("max_edges", c_int32),
+                ("params", c_void_p), ("grads", c_void_p)]
+
+
+GRAD_READY_FN = ctypes.CFUNCTYPE(None, c_void_p, c_int32, c_size_t, c_size_t)
+
+
 class gm_pack_job(ctypes.Structure):
     _fields_ = [("w", c_void_p), ("ld", c_int32), ("col0", c_int32), ("transpose", c_int32), ("chunk", c_void_p)]
 
@@ -122,6 +131,19 @@ SIGNATURES = {
                                         c_void_p]),
     "gm_adam_step": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_float, c_float, c_float,
                                     c_float, c_int32, c_void_p]),
+    "gm_train_workspace_bytes": (c_size_t, [POINTER(gm_train_desc)]),
+    "gm_train_create": (ctypes.c_int, [POINTER(c_void_p), POINTER(gm_train_desc), c_void_p, c_size_t, c_void_p]),
+    "gm_train_destroy": (None, [c_void_p]),
+    "gm_train_sync_weights": (ctypes.c_int, [c_void_p, c_void_p]),
+    "gm_train_num_buckets": (c_int32, [c_void_p]),
+    "gm_train_bucket": (ctypes.c_int, [c_void_p, c_int32, POINTER(c_size_t), POINTER(c_size_t)]),
+    "gm_train_prediction": (c_void_p, [c_void_p]),
+    "gm_train_forward_backward": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_double, c_int32, c_int32] +
+                                  [c_void_p] * 9 + [c_int32, c_void_p, c_void_p, c_void_p]),
+    "gm_random_walk_noise": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, POINTER(gm_phys), c_void_p, c_double,
+                                            ctypes.c_uint64, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "gm_training_target": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, POINTER(gm_phys), c_void_p, c_void_p,
+                                          c_void_p]),
     "gm_debug_stamps": (ctypes.c_int, [c_void_p, c_int32]),
     "gm_selftest_gemm": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),
     "gm_selftest_gemm_ts": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),

@@ -8,7 +8,8 @@ import torch
 
 from . import _lib
 from ._lib import check, ptr, stream_ptr
-from .utils import compute_acceleration, get_edges_displacement, get_nodes_vel, radius_graph
+from .utils import (compute_acceleration, get_edges_displacement, get_nodes_vel, radius_graph,
+                    random_walk_noise)
 
 
 class GraphAttributes:
@@ -41,9 +42,28 @@ class GraphAttributes:
         nodes_tgt = self.compute_target(obs, tgt)
         return nodes, edge_attr, senders, receivers, nodes_tgt
 
+    def _noisy(self, obs, tgt):
+        """collate_utils.py:41-56 / 169-183: (noisy_obs, noisy_tgt) -- random-walk noise on the cartesian columns, its last
+        frame added to the target."""
+        pos_seq = obs[:, :, self.cartesian_idx]
+        noise = random_walk_noise(pos_seq, self.noise_std).to(obs.device)
+        noisy_obs = obs.clone()
+        noisy_obs[:, :, self.cartesian_idx] = obs[:, :, self.cartesian_idx] + noise
+        return noisy_obs, tgt + noise[-1]
+
     def _process_noisy(self, obs, tgt):
-        # random_walk_noise (gnn_manip/utils/utils.py:96-115) belongs to the training data path, SURVEY.md row N3
-        raise NotImplementedError("noise_std != None (training-time random-walk noise) is not part of the rollout path")
+        """collate_utils.py:41-66 (the base class drops max_neighbours here too: cap 20)."""
+        noisy_obs, noisy_tgt = self._noisy(obs, tgt)
+        out_dev = obs.device
+        last_pos = noisy_obs[-1][:, self.cartesian_idx]
+        nodes = self.compute_nodes(noisy_obs)
+        ei = radius_graph(last_pos, self.conn_r, self._noisy_max_neighbours()).edge_index()
+        senders, receivers = ei[0].to(out_dev), ei[1].to(out_dev)
+        edge_attr = self.compute_edges(noisy_obs, senders, receivers)
+        return nodes, edge_attr, senders, receivers, self.compute_target(noisy_obs, noisy_tgt)
+
+    def _noisy_max_neighbours(self):
+        return self._simple_max_neighbours
 
     def process_collate(self, batch):
         """collate_utils.py:68-87: concatenates per-sample graphs with node offset N*i (equal N per sample)."""
@@ -101,6 +121,9 @@ class GraphBoundedMultimaterial(GraphSimple):
         super().__init__(conn_r, stats, cartesian_idx, None, bounds, noise)
 
     _control_idx = None
+
+    def _noisy_max_neighbours(self):
+        return self.max_neighbours           # collate_utils.py:187: the noisy path of this class does pass the cap
 
     def phys(self):
         return _lib.make_phys(self.conn_r, self.stats, self.bounds, self.cartesian_idx, self.material_idx,

@@ -867,6 +867,20 @@ int gm_rigid_trajectory(const double* rot, const double* ty, int32_t n_cand, int
   return rigid_trajectory(rot, ty, n_cand, steps, rigid_init, n_rigid, ty_init_host, out, (cudaStream_t)stream);
 }
 
+int gm_random_walk_noise(const float* obs, int32_t k, int32_t n, int32_t D, const gm_phys* phys, const float* tgt,
+                         double noise_std, uint64_t seed, float* noisy_obs, float* noisy_tgt, float* samples,
+                         void* stream) {
+  GM_REQUIRE(phys != nullptr, "gm_random_walk_noise: phys is NULL");
+  return random_walk_noise(obs, k, n, D, to_phys(*phys, k), tgt, noise_std, (unsigned long long)seed, noisy_obs,
+                           noisy_tgt, samples, (cudaStream_t)stream);
+}
+
+int gm_training_target(const float* obs, int32_t k, int32_t n, int32_t D, const gm_phys* phys, const float* tgt,
+                       float* target, void* stream) {
+  GM_REQUIRE(phys != nullptr, "gm_training_target: phys is NULL");
+  return training_target(obs, k, n, D, to_phys(*phys, k), tgt, target, (cudaStream_t)stream);
+}
+
 size_t gm_sinkhorn_workspace_bytes(int32_t n_batch, int32_t n, int32_t m) {
   if (n_batch <= 0 || n <= 0 || m <= 0) return 0;
   return sinkhorn_workspace_bytes(n_batch, n, m);
@@ -939,7 +953,7 @@ size_t gm_train_small_partial_bytes(int32_t n_rows, int32_t K, int32_t O) {
 
 int gm_train_small_bwd(const float* x, int32_t K, const float* w, int32_t O, const float* dh, const float* mask,
                        int32_t n_rows, float* dW, float* db, float* dx, void* partial, void* stream) {
-  return tr_small_bwd(x, K, w, O, dh, mask, n_rows, nullptr, dW, db, dx, (float*)partial, (cudaStream_t)stream);
+  return tr_small_bwd(x, K, w, O, dh, mask, n_rows, nullptr, dW, db, dx, nullptr, (float*)partial, (cudaStream_t)stream);
 }
 
 int gm_train_l1_loss(const float* pred, const float* tgt, const uint8_t* row_mask, int32_t n_rows, int32_t width,

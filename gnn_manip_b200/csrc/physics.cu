@@ -10,6 +10,8 @@
 // (true division, sqrt.rn), so node features and the integrator are bit-identical to the CPU
 // reference; the edge norm uses the fused accumulation torch.norm performs on CPU.
 #include <string.h>
+#include <math.h>
+#include <curand_kernel.h>
 #include "common.cuh"
 #include "physics.cuh"
 
@@ -92,6 +94,52 @@ __global__ void rigid_trajectory_kernel(RolloutParams rp, int steps, float* __re
   float tgt[3];
   rigid_target(rp, g, r, step, tgt);
   out[idx * 3 + 0] = tgt[0]; out[idx * 3 + 1] = tgt[1]; out[idx * 3 + 2] = tgt[2];
+}
+
+// Row N3: random_walk_noise (utils.py:96-115) + the noisy observation / target of _process_noisy (collate_utils.py:169-193).
+// One thread per (particle, axis): k-1 normal draws, two running sums.
+__global__ void random_walk_noise_kernel(const float* __restrict__ obs, int k, int n, int D, PhysParams p,
+                                         const float* __restrict__ tgt, float step_std, unsigned long long seed,
+                                         float* __restrict__ noisy_obs, float* __restrict__ noisy_tgt,
+                                         float* __restrict__ samples) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n * 3) return;
+  const int node = idx / 3, d = idx - 3 * node;
+  curandStatePhilox4_32_10_t st;
+  curand_init(seed, (unsigned long long)idx, 0ull, &st);
+  float vel = 0.f, posn = 0.f;
+  // frame 0 carries no noise (utils.py:111-113)
+  for (int t = 0; t < k; ++t) {
+    if (t > 0) {
+      const float z = curand_normal(&st) * step_std;
+      if (samples) samples[((size_t)(t - 1) * n + node) * 3 + d] = z;
+      vel = __fadd_rn(vel, z);              // torch.cumsum over the velocity noise
+      posn = __fadd_rn(posn, vel);          // torch.cumsum over the noisy velocity
+    }
+    const size_t o = ((size_t)t * n + node) * D + p.cart[d];
+    noisy_obs[o] = __fadd_rn(obs[o], posn);
+  }
+  if (noisy_tgt) noisy_tgt[idx] = __fadd_rn(tgt[idx], posn);
+}
+
+__global__ void copy_non_cartesian_kernel(const float* __restrict__ obs, long long total, int D, PhysParams p,
+                                          float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c = (int)(i % D);
+  if (c != p.cart[0] && c != p.cart[1] && c != p.cart[2]) out[i] = obs[i];
+}
+
+// compute_target (collate_utils.py:148-157) over compute_acceleration (utils.py:10-24)
+__global__ void training_target_kernel(const float* __restrict__ obs, int k, int n, int D, PhysParams p,
+                                       const float* __restrict__ tgt, float* __restrict__ target) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n * 3) return;
+  const int node = idx / 3, d = idx - 3 * node;
+  const float p1 = obs[((size_t)(k - 1) * n + node) * D + p.cart[d]];
+  const float p2 = obs[((size_t)(k - 2) * n + node) * D + p.cart[d]];
+  const float acc = __fadd_rn(__fsub_rn(tgt[idx], __fmul_rn(2.0f, p1)), p2);
+  target[idx] = __fdiv_rn(__fsub_rn(acc, p.acc_mean[d]), p.acc_std[d]);
 }
 
 // Step (1) of the loop body: control columns of the rigid particles (traj_utils.py:126-135).
@@ -215,6 +263,32 @@ int rigid_trajectory(const double* rot, const double* ty, int n_cand, int steps,
   rigid_trajectory_kernel<<<ceil_div(total, 256), 256, 0, stream>>>(rp, steps, out);
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("rigid_trajectory_kernel");
+  return GM_OK;
+}
+
+int random_walk_noise(const float* obs, int k, int n, int D, const PhysParams& p, const float* tgt, double noise_std,
+                      unsigned long long seed, float* noisy_obs, float* noisy_tgt, float* samples, cudaStream_t stream) {
+  GM_REQUIRE(obs != nullptr && noisy_obs != nullptr && k >= 2 && n > 0 && D >= 3, "random_walk_noise: bad arguments");
+  GM_REQUIRE(noisy_tgt == nullptr || tgt != nullptr, "random_walk_noise: noisy_tgt needs tgt");
+  const long long total = (long long)k * n * D;
+  if (noisy_obs != obs) {
+    copy_non_cartesian_kernel<<<ceil_div(total, 256), 256, 0, stream>>>(obs, total, D, p, noisy_obs);
+    GM_LAUNCHED(1);
+  }
+  const float step_std = (float)(noise_std / sqrt((double)(k - 1)));     // utils.py:103
+  random_walk_noise_kernel<<<ceil_div((long long)n * 3, 128), 128, 0, stream>>>(obs, k, n, D, p, tgt, step_std, seed,
+                                                                            noisy_obs, noisy_tgt, samples);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("random_walk_noise kernels");
+  return GM_OK;
+}
+
+int training_target(const float* obs, int k, int n, int D, const PhysParams& p, const float* tgt, float* target,
+                    cudaStream_t stream) {
+  GM_REQUIRE(obs != nullptr && tgt != nullptr && target != nullptr && k >= 2 && n > 0, "training_target: bad arguments");
+  training_target_kernel<<<ceil_div((long long)n * 3, 256), 256, 0, stream>>>(obs, k, n, D, p, tgt, target);
+  GM_LAUNCHED(1);
+  GM_LAUNCH_CHECK("training_target_kernel");
   return GM_OK;
 }
 

@@ -37,6 +37,10 @@ int edge_features(const float* pos, int stride, const int* send, const int* recv
 int apply_control(float* obs, const RolloutParams& rp, cudaStream_t stream);
 int rigid_trajectory(const double* rot, const double* ty, int n_cand, int steps, const float* rigid_init, int n_rigid,
                      const float ty_init[3], float* out, cudaStream_t stream);
+int random_walk_noise(const float* obs, int k, int n, int D, const PhysParams& p, const float* tgt, double noise_std,
+                      unsigned long long seed, float* noisy_obs, float* noisy_tgt, float* samples, cudaStream_t stream);
+int training_target(const float* obs, int k, int n, int D, const PhysParams& p, const float* tgt, float* target,
+                    cudaStream_t stream);
 int integrate(float* obs, const float* pred, const RolloutParams& rp, float* next_pos_out, cudaStream_t stream);
 
 #ifdef __CUDACC__

@@ -58,12 +58,13 @@ int tr_ln_bwd(const float* d1, const float* d2, const int* idx2, const float* xh
 // Small first / last layers on CUDA cores.
 //   fwd:  h[r, o] = act(x[r, :K] . w[o, :K] + b[o])   (w [O][K] row-major, K, O <= 128)
 //   bwd:  dz = mask ? dh (mask > 0) : dh;  dW[o, k] += sum_r dz[r, o] x[r, k];  db[o] += sum_r dz[r, o];
-//         dx[r, k] = sum_o dz[r, o] w[o, k] (optional)
+//         dx[r, k] = sum_o dz[r, o] w[o, k] (optional), zeroed where dx_mask[r, k] <= 0 (optional: ReLU of the layer below)
 int tr_small_fwd(const float* x, int K, const float* w, const float* b, int O, int M, const int* M_dev, int relu,
                  float* h, cudaStream_t stream);
 size_t tr_small_partial_floats(int M, int K, int O);
 int tr_small_bwd(const float* x, int K, const float* w, int O, const float* dh, const float* mask, int M,
-                 const int* M_dev, float* dW, float* db, float* dx, float* partial, cudaStream_t stream);
+                 const int* M_dev, float* dW, float* db, float* dx, const float* dx_mask, float* partial,
+                 cudaStream_t stream);
 
 // L1Loss(reduction='sum') / n_rows (examples/train_dyn.py:56-64, 109): loss scalar (device) and dpred = sign(pred - tgt) / n
 // over the rows selected by row_mask (null = all rows; the `use_updated_loss` variant keeps sand rows only)

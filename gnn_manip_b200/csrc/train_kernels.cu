@@ -530,7 +530,7 @@ tr_small_fwd_kernel(const float* __restrict__ x, int K, const float* __restrict_
 __global__ void __launch_bounds__(256)
 tr_small_bwd_kernel(const float* __restrict__ x, int K, const float* __restrict__ w, int O, const float* __restrict__ dh,
                     const float* __restrict__ mask, int M_max, const int* __restrict__ M_dev, float* __restrict__ dx,
-                    float* __restrict__ partial) {
+                    const float* __restrict__ dx_mask, float* __restrict__ partial) {
   extern __shared__ float s_small[];
   float* sx = s_small;                       // [rows][K]
   float* sd = s_small + kSmallRows * K;      // [rows][O]
@@ -562,6 +562,7 @@ tr_small_bwd_kernel(const float* __restrict__ x, int K, const float* __restrict_
       const int r = i / K, k = i - r * K;
       float acc = 0.f;
       for (int o = 0; o < O; ++o) acc = fmaf(sd[r * O + o], sw[o * K + k], acc);
+      if (dx_mask && !(dx_mask[(size_t)(row0 + r) * K + k] > 0.f)) acc = 0.f;
       dx[(size_t)(row0 + r) * K + k] = acc;
     }
   }
@@ -677,7 +678,8 @@ int tr_small_fwd(const float* x, int K, const float* w, const float* b, int O, i
 size_t tr_small_partial_floats(int M, int K, int O) { return (size_t)ceil_div(M > 0 ? M : 1, kSmallRows) * (O * K + O); }
 
 int tr_small_bwd(const float* x, int K, const float* w, int O, const float* dh, const float* mask, int M,
-                 const int* M_dev, float* dW, float* db, float* dx, float* partial, cudaStream_t stream) {
+                 const int* M_dev, float* dW, float* db, float* dx, const float* dx_mask, float* partial,
+                 cudaStream_t stream) {
   if (M <= 0) return GM_OK;
   const size_t smem = sizeof(float) * ((size_t)kSmallRows * K + (size_t)kSmallRows * O + (dx ? (size_t)O * K : 0));
   GM_REQUIRE(smem <= 96 * 1024, "tr_small_bwd: K=%d O=%d need %zu bytes of shared memory", K, O, smem);
@@ -688,7 +690,7 @@ int tr_small_bwd(const float* x, int K, const float* w, int O, const float* dh, 
     once.finish(dev);
   }
   const int nb = ceil_div(M, kSmallRows), width = O * K + O;
-  tr_small_bwd_kernel<<<nb, 256, smem, stream>>>(x, K, w, O, dh, mask, M, M_dev, dx, partial);
+  tr_small_bwd_kernel<<<nb, 256, smem, stream>>>(x, K, w, O, dh, mask, M, M_dev, dx, dx_mask, partial);
   tr_partial_reduce_kernel<<<ceil_div(width, 256), 256, 0, stream>>>(partial, nb, kSmallRows, M_dev, width, dW, db, O * K);
   GM_LAUNCHED(2);
   GM_LAUNCH_CHECK("tr_small_bwd kernels");

@@ -122,3 +122,34 @@ def get_edges_displacement(last_pos, senders, receivers, conn_r):
             check(_lib.lib().gm_edge_features(ptr(p), 3, ptr(s), ptr(r), None, E, float(conn_r), ptr(out),
                                               stream_ptr(dev)), "gm_edge_features")
     return out.to(out_dev)
+
+
+_noise_calls = [0]
+
+
+def random_walk_noise(pos_seq, noise_std, seed=None, return_samples=False):
+    """gnn_manip/utils/utils.py:96-115: position noise [k, N, 3] of a random walk in velocity whose last-step velocity
+    noise has standard deviation `noise_std` (zero noise on the first frame).  Drawn on the device with Philox4x32-10
+    (the reference samples torch.distributions.Normal on the CPU: same distribution, different stream).  `seed`
+    defaults to torch.initial_seed() advanced by one per call."""
+    import ctypes
+    out_dev = pos_seq.device
+    dev = _lib.compute_device(pos_seq)
+    p = pos_seq.to(device=dev, dtype=torch.float32).contiguous()
+    k, n, d = p.shape
+    if d != 3:
+        raise ValueError("random_walk_noise expects [k, N, 3] positions")
+    if seed is None:
+        seed = (torch.initial_seed() + _noise_calls[0]) & 0xFFFFFFFFFFFFFFFF
+        _noise_calls[0] += 1
+    phys = _lib.make_phys(1.0, None, None, [0, 1, 2], 0, None)
+    zeros = torch.zeros_like(p)
+    noisy = torch.empty_like(p)
+    samples = torch.empty((k - 1, n, 3), dtype=torch.float32, device=dev) if return_samples else None
+    with torch.cuda.device(dev):
+        check(_lib.lib().gm_random_walk_noise(ptr(zeros), k, n, 3, ctypes.byref(phys), None, float(noise_std),
+                                              ctypes.c_uint64(int(seed)), ptr(noisy), None, ptr(samples),
+                                              stream_ptr(dev)), "gm_random_walk_noise")
+    if return_samples:
+        return noisy.to(out_dev), samples.to(out_dev)
+    return noisy.to(out_dev)

@@ -297,6 +297,54 @@ int gm_train_l1_loss(const float* pred, const float* tgt, const uint8_t* row_mas
 int gm_adam_step(float* params, const float* grads, float* m, float* v, size_t n, float lr, float beta1, float beta2,
                  float eps, int32_t step, void* stream);
 
+/* ---- the training step itself ---------------------------------------------------------------------------------
+ * A plan owns the packed operand chunks of every 128 x 128 weight block (forward and transposed), the saved
+ * activations of one batch and the backward scratch, all inside the caller's workspace.  params / grads: flat fp32
+ * vectors in gm_model_create's parameter order (the optimiser updates params in place; call gm_train_sync_weights
+ * afterwards).  Covers hidden = 128, num_layers = 2 (the reference configuration, rollout_utils.py:133-134). */
+typedef struct gm_train gm_train;
+typedef struct gm_train_desc {
+  int32_t node_dim, edge_dim, out_dim, hidden, num_layers, m_steps;
+  int32_t max_nodes, max_edges;     /* largest batch: nodes, edge slots (nodes * max_neighbours) */
+  float* params;                    /* [gm_model_num_params] device */
+  float* grads;                     /* same length, device: overwritten by every backward */
+} gm_train_desc;
+size_t gm_train_workspace_bytes(const gm_train_desc* desc_host);
+int gm_train_create(gm_train** plan, const gm_train_desc* desc_host, void* workspace /*1024-byte aligned*/,
+                    size_t workspace_bytes, void* stream);
+void gm_train_destroy(gm_train* plan);
+int gm_train_sync_weights(gm_train* plan, void* stream);
+/* gradient buckets in the order the backward completes them (decoder, processor blocks m-1 .. 0, encoders): bucket b
+ * is grads[offset, offset + count) */
+int32_t gm_train_num_buckets(const gm_train* plan);
+int gm_train_bucket(const gm_train* plan, int32_t bucket, size_t* offset_host, size_t* count_host);
+const float* gm_train_prediction(const gm_train* plan);     /* [n_nodes, out_dim] of the last forward (device) */
+/* loss_batch (examples/train_dyn.py:49-72) without the optimiser step: forward on a batch of graphs given as one
+ * disjoint graph (nodes [n, node_dim]; positions for the edge features; the receiver-major edge list of
+ * gm_radius_graph: recv_ptr, esend, erecv, eref; edge_ptr = its sender-major offsets), loss = L1Loss(sum) / rows over
+ * the rows row_mask selects (NULL = all), and -- with_backward -- every parameter gradient into grads.
+ * grad_ready (optional, host callback) fires right after the kernels that complete bucket b were enqueued, so the
+ * caller can order a collective on that slice behind them.  Everything is enqueued on `stream`. */
+typedef void (*gm_grad_ready_fn)(void* user, int32_t bucket, size_t offset, size_t count);
+int gm_train_forward_backward(gm_train* plan, const float* nodes, const float* pos, int32_t pos_stride, double conn_r,
+                              int32_t n_nodes, int32_t max_edges, const int32_t* n_edges_dev, const int32_t* recv_ptr,
+                              const int32_t* esend, const int32_t* erecv, const int32_t* eref, const int32_t* edge_ptr,
+                              const float* target, const uint8_t* row_mask, float* loss, int32_t with_backward,
+                              gm_grad_ready_fn grad_ready, void* user, void* stream);
+
+/* ---- Row N3: training data path on the device -----------------------------------------------------------------
+ * random_walk_noise (gnn_manip/utils/utils.py:96-115) + GraphBoundedMultimaterial._process_noisy
+ * (collate_utils.py:169-193): per particle and cartesian axis, k-1 Normal(0, noise_std / sqrt(k-1)) velocity
+ * increments (Philox4x32-10 keyed by seed, particle and axis), accumulated twice (velocity, then position); the
+ * position noise is added to the cartesian columns of obs (first frame untouched) and its last frame to tgt.
+ * samples (optional) [k-1, n, 3]: the raw normal draws, for tests. */
+int gm_random_walk_noise(const float* obs, int32_t k, int32_t n, int32_t D, const gm_phys* phys, const float* tgt,
+                         double noise_std, uint64_t seed, float* noisy_obs, float* noisy_tgt, float* samples,
+                         void* stream);
+/* compute_target (collate_utils.py:148-157): ((tgt - 2 p[-1] + p[-2]) - acc_mean) / acc_std -> [n, 3] */
+int gm_training_target(const float* obs, int32_t k, int32_t n, int32_t D, const gm_phys* phys, const float* tgt,
+                       float* target, void* stream);
+
 /* Debug aid: phase timestamps (clock64) recorded by CTA 0 of the instrumented kernels; only in -DGM_STAMPS builds
  * (returns GM_STATUS_UNSUPPORTED otherwise).  out_host: host array of n <= 64 values. */
 int gm_debug_stamps(unsigned long long* out_host, int32_t n);
