@@ -138,6 +138,7 @@ SIGNATURES = {
     "gm_train_num_buckets": (c_int32, [c_void_p]),
     "gm_train_bucket": (ctypes.c_int, [c_void_p, c_int32, POINTER(c_size_t), POINTER(c_size_t)]),
     "gm_train_prediction": (c_void_p, [c_void_p]),
+    "gm_train_activation": (c_void_p, [c_void_p, c_int32, c_int32]),
     "gm_train_forward_backward": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_double, c_int32, c_int32] +
                                   [c_void_p] * 9 + [c_int32, c_void_p, c_void_p, c_void_p]),
     "gm_random_walk_noise": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, POINTER(gm_phys), c_void_p, c_double,

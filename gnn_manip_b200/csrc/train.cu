@@ -265,6 +265,24 @@ int gm_train_bucket(const gm_train* t, int32_t bucket, size_t* offset, size_t* c
 
 const float* gm_train_prediction(const gm_train* t) { return t ? t->pred : nullptr; }
 
+const float* gm_train_activation(const gm_train* t, int32_t which, int32_t step) {
+  if (!t) return nullptr;
+  const bool step_ok = step >= 0 && step < t->d.m_steps;
+  switch (which) {
+    case 0: return t->ee_h1;
+    case 1: return t->ee_h2;
+    case 2: return t->en_h1;
+    case 3: return t->en_h2;
+    case 4: return step_ok ? t->act[step].eh1 : nullptr;
+    case 5: return step_ok ? t->act[step].eh2 : nullptr;
+    case 6: return step_ok ? t->act[step].nh1 : nullptr;
+    case 7: return step_ok ? t->act[step].nh2 : nullptr;
+    case 8: return t->dc_h1;
+    case 9: return t->dc_h2;
+    default: return nullptr;
+  }
+}
+
 }  // extern "C"
 
 // =====================================================================================================

@@ -208,6 +208,12 @@ class Trainer:
         nbytes = n_rows * self.model.out_dim * 4
         return self.workspace[addr - base: addr - base + nbytes].view(torch.float32).reshape(n_rows, -1).clone()
 
+    def activation(self, which, step, n_rows):
+        """Test aid: a copy of a saved post-ReLU activation [n_rows, 128] (gm_train_activation)."""
+        addr = _lib.lib().gm_train_activation(self.handle, int(which), int(step))
+        base = self.workspace.data_ptr()
+        return self.workspace[addr - base: addr - base + n_rows * 128 * 4].view(torch.float32).reshape(n_rows, 128).clone()
+
     def export_to(self, model=None):
         """Write the flat parameters back into the nn.Module (state-dict layout unchanged: torch.save works as in
         train_dyn.py:20-22)."""

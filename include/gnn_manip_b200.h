@@ -319,6 +319,10 @@ int gm_train_sync_weights(gm_train* plan, void* stream);
 int32_t gm_train_num_buckets(const gm_train* plan);
 int gm_train_bucket(const gm_train* plan, int32_t bucket, size_t* offset_host, size_t* count_host);
 const float* gm_train_prediction(const gm_train* plan);     /* [n_nodes, out_dim] of the last forward (device) */
+/* test aid: the saved post-ReLU activations [rows, 128] of the last forward (edges in receiver-major order).
+ * which: 0/1 edge encoder h1/h2, 2/3 node encoder h1/h2, 4/5 edge MLP h1/h2 of `step`, 6/7 node MLP h1/h2 of `step`,
+ * 8/9 decoder h1/h2 */
+const float* gm_train_activation(const gm_train* plan, int32_t which, int32_t step);
 /* loss_batch (examples/train_dyn.py:49-72) without the optimiser step: forward on a batch of graphs given as one
  * disjoint graph (nodes [n, node_dim]; positions for the edge features; the receiver-major edge list of
  * gm_radius_graph: recv_ptr, esend, erecv, eref; edge_ptr = its sender-major offsets), loss = L1Loss(sum) / rows over
