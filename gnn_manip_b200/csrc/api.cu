@@ -1,6 +1,7 @@
 // C ABI (include/gnn_manip_b200.h): model packing, forward orchestration, rollout plan + CUDA graph.
 #include <math.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 #include <new>
 #include <vector>
@@ -306,9 +307,13 @@ int forward_tc(const gm_model* m, const float* nodes, const float* edge_attr, co
     if ((rc = tc_mp_edge(m->tc_proc_edge[s], g, b, st, !(s == 0 && enc_node_done != nullptr)))) return rc;
     GM_PROF(kProfMpNode);
     const bool last = s + 1 == m->m_steps;
-    if ((rc = tc_mp_node(m->tc_proc_node[s], last ? nullptr : &m->tc_proc_edge[s + 1], last ? &m->tc_dec : nullptr,
-                         m->out_dim, pred, g, b, st)))
-      return rc;
+    // node half: the 16-warp kernel (mp_node16.cu); GM_NODE_KERNEL=8 selects the 8-warp kernel of mp_tc.cu (A/B aid)
+    static const bool node8 = [] { const char* e = getenv("GM_NODE_KERNEL"); return e && !strcmp(e, "8"); }();
+    rc = node8 ? tc_mp_node(m->tc_proc_node[s], last ? nullptr : &m->tc_proc_edge[s + 1], last ? &m->tc_dec : nullptr,
+                            m->out_dim, pred, g, b, st)
+               : tc_mp_node16(m->tc_proc_node[s], last ? nullptr : &m->tc_proc_edge[s + 1], last ? &m->tc_dec : nullptr,
+                              m->out_dim, pred, g, b, st);
+    if (rc) return rc;
   }
   GM_PROF(-1);
   return GM_OK;
@@ -527,6 +532,7 @@ int gm_model_create(gm_model** out, const float* flat_params, size_t n_params, i
   {
     int rc0 = mlp_simt_configure();
     if (!rc0 && shape_supports_tc(node_dim, edge_dim, out_dim, hidden, num_layers)) rc0 = tc_configure();
+    if (!rc0 && shape_supports_tc(node_dim, edge_dim, out_dim, hidden, num_layers)) rc0 = tc_configure_node16();
     if (rc0) return rc0;
   }
   gm_model* m = new (std::nothrow) gm_model();

@@ -60,6 +60,11 @@ int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_
 int tc_mp_node(const TcMlp& m, const TcMlp* next_edge, const TcMlp* dec, int out_dim, float* pred,
                const TcGraph& g, const TcBuffers& b, cudaStream_t stream);
 
+// The same node half with 16 warps per tile (thread = row x 32 columns; mp_node16.cu): shorter epilogues per GEMM.
+int tc_configure_node16();
+int tc_mp_node16(const TcMlp& m, const TcMlp* next_edge, const TcMlp* dec, int out_dim, float* pred, const TcGraph& g,
+                 const TcBuffers& b, cudaStream_t stream);
+
 // Pack W[n_out=128][ld] columns [col0, col0+128) (fp32, row-major) into one 64 KB chunk image.
 int tc_pack_chunk(const float* w, int ld, int col0, void* chunk, cudaStream_t stream);
 
