@@ -17,6 +17,7 @@
 // The receiver-major order is what the message-passing kernels consume: a receiver's incoming edges are
 // contiguous, so the scatter_add of graph_networks.py:75-85 becomes a deterministic segmented sum that
 // visits the edges of each receiver in ascending reference edge id (the CPU order of index_add_).
+#include <stdlib.h>
 #include "common.cuh"
 #include "scan.cuh"
 #include "radius_graph.cuh"
@@ -28,6 +29,8 @@ namespace {
 struct GridParams {
   double lo[3];
   double cs;        // cell edge (>= r * (1 + 1e-6))
+  double inv_cs;    // 1 / cs: the cell index is floor((p - lo) * inv_cs) -- monotone in p like the quotient, and every
+                    // kernel uses this one expression, so |dx| <= r < cs still never skips a cell
   int dim[3];
   int cells_per_graph;
 };
@@ -101,6 +104,7 @@ __device__ void grid_setup_body(const unsigned* bbox, double r, int n_graphs, in
     gp->dim[d] = dim[d];
   }
   gp->cs = cs;
+  gp->inv_cs = 1.0 / cs;
   gp->cells_per_graph = dim[0] * dim[1] * dim[2];
 }
 
@@ -108,6 +112,130 @@ __global__ void grid_setup_kernel(const unsigned* __restrict__ bbox, double r, i
                                   GridParams* __restrict__ gp) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   grid_setup_body(bbox, r, n_graphs, max_cells, gp);
+}
+
+__device__ __forceinline__ void cell_coords(const GridParams& gp, float x, float y, float z, int c[3]) {
+  const float p[3] = {x, y, z};
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    // fp64 keeps floor((p - lo) / cs) monotone, so |dx| <= r < cs never skips a cell (a multiplication by 1 / cs:
+    // fp64 division is microcoded and dominated the single-block cell-list kernel)
+    int v = (int)floor(((double)p[d] - gp.lo[d]) * gp.inv_cs);
+    c[d] = min(max(v, 0), gp.dim[d] - 1);
+  }
+}
+
+// Tiny inputs (n <= kTinyN, e.g. one 2 000-particle rollout): ONE block builds the whole cell list -- bounding box, grid
+// set-up, per-cell counts and their exclusive scan in shared memory, cell-sorted positions -- and clears the in-degree /
+// fill counters and the tail ticket of the neighbour kernel (replaces prepare_small + cell_count + scan + cell_fill).
+constexpr int kTinyN = 8192;
+constexpr int kTinyCells = 8192;
+constexpr int kTinyThreads = 1024;
+constexpr int kTinyPer = kTinyN / kTinyThreads;       // particles per thread
+
+__global__ void __launch_bounds__(kTinyThreads)
+cell_list_tiny_kernel(const float* __restrict__ pos, int stride, int n, int n_per_graph, double r, int n_graphs,
+                      int max_cells /*capacity of cell_start - 2*/, GridParams* __restrict__ gp_out, int* __restrict__ cell_start, float4* __restrict__ sorted,
+                      int* __restrict__ indeg_fill /*2(n+1)*/, int* __restrict__ tail_ticket) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
+  __shared__ unsigned s_box[6];
+  __shared__ GridParams s_gp;
+  __shared__ int s_cnt[kTinyCells];
+  __shared__ int s_warp[kTinyThreads / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < 3) s_box[tid] = 0xFFFFFFFFu;
+  else if (tid < 6) s_box[tid] = 0u;
+  __syncthreads();
+  float px[kTinyPer], py[kTinyPer], pz[kTinyPer];
+  unsigned mn[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, mx[3] = {0u, 0u, 0u};
+#pragma unroll
+  for (int k = 0; k < kTinyPer; ++k) {
+    const int i = tid + k * kTinyThreads;
+    px[k] = py[k] = pz[k] = 0.f;
+    if (i < n) {
+      const float* p = pos + (size_t)i * stride;
+      px[k] = p[0]; py[k] = p[1]; pz[k] = p[2];
+      const unsigned o[3] = {f2ord(px[k]), f2ord(py[k]), f2ord(pz[k])};
+#pragma unroll
+      for (int d = 0; d < 3; ++d) { mn[d] = min(mn[d], o[d]); mx[d] = max(mx[d], o[d]); }
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[d] = min(mn[d], __shfl_xor_sync(0xffffffffu, mn[d], o));
+      mx[d] = max(mx[d], __shfl_xor_sync(0xffffffffu, mx[d], o));
+    }
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) { atomicMin(&s_box[d], mn[d]); atomicMax(&s_box[3 + d], mx[d]); }
+  }
+  for (int i = tid; i < kTinyCells; i += kTinyThreads) s_cnt[i] = 0;
+  for (int i = tid; i < 2 * (n + 1); i += kTinyThreads) indeg_fill[i] = 0;
+  if (tid == 0) *tail_ticket = 0;
+  __syncthreads();
+  if (tid == 0) {
+    grid_setup_body(s_box, r, n_graphs, min(kTinyCells, max_cells), &s_gp);   // cells <= both the shared counters and cell_start
+    *gp_out = s_gp;
+  }
+  __syncthreads();
+  const GridParams gp = s_gp;
+  const int cells = gp.cells_per_graph * n_graphs;      // <= kTinyCells by construction of the grid
+  int cell[kTinyPer];
+#pragma unroll
+  for (int k = 0; k < kTinyPer; ++k) {
+    const int i = tid + k * kTinyThreads;
+    cell[k] = -1;
+    if (i < n) {
+      int c[3];
+      cell_coords(gp, px[k], py[k], pz[k], c);
+      cell[k] = (i / n_per_graph) * gp.cells_per_graph + (c[2] * gp.dim[1] + c[1]) * gp.dim[0] + c[0];
+      atomicAdd(&s_cnt[cell[k]], 1);
+    }
+  }
+  __syncthreads();
+  // exclusive scan of s_cnt[0 .. cells): 8 consecutive cells per thread
+  {
+    constexpr int kPerT = kTinyCells / kTinyThreads;
+    int v[kPerT], sum = 0;
+#pragma unroll
+    for (int k = 0; k < kPerT; ++k) { v[k] = s_cnt[tid * kPerT + k]; sum += v[k]; }
+    int x = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) s_warp[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      int w = s_warp[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += y;
+      }
+      s_warp[lane] = w;
+    }
+    __syncthreads();
+    int ex = (warp == 0 ? 0 : s_warp[warp - 1]) + x - sum;
+#pragma unroll
+    for (int k = 0; k < kPerT; ++k) {
+      const int c = tid * kPerT + k;
+      s_cnt[c] = ex;                                   // becomes the fill cursor of the cell
+      if (c <= cells) cell_start[c] = ex;              // cell_start[cells] == n
+      ex += v[k];
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < kTinyPer; ++k) {
+    const int i = tid + k * kTinyThreads;
+    if (i < n) sorted[atomicAdd(&s_cnt[cell[k]], 1)] = make_float4(px[k], py[k], pz[k], __int_as_float(i));
+  }
 }
 
 // Small inputs (n <= kSmallN): one block computes the bounding box, sets the grid up and zeroes the counters
@@ -152,16 +280,6 @@ prepare_small_kernel(const float* __restrict__ pos, int stride, int n, double r,
   for (int i = threadIdx.x; i < 2 * (n + 1); i += blockDim.x) indeg_fill[i] = 0;
   __syncthreads();
   if (threadIdx.x == 0) grid_setup_body(s_box, r, n_graphs, max_cells, gp);
-}
-
-__device__ __forceinline__ void cell_coords(const GridParams& gp, float x, float y, float z, int c[3]) {
-  const float p[3] = {x, y, z};
-#pragma unroll
-  for (int d = 0; d < 3; ++d) {
-    // fp64 keeps floor((p - lo)/cs) monotone, so |dx| <= r < cs never skips a cell
-    int v = (int)floor(((double)p[d] - gp.lo[d]) / gp.cs);
-    c[d] = min(max(v, 0), gp.dim[d] - 1);
-  }
 }
 
 __global__ void cell_count_kernel(const float* __restrict__ pos, int stride, int n, int n_per_graph,
@@ -244,14 +362,16 @@ __device__ __forceinline__ int warp_select_smallest(const double* bd, const int*
 __global__ void __launch_bounds__(kNbrWarps * 32)
 neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                  const GridParams* __restrict__ gpp, int n, int n_per_graph, double r2, int K,
-                 int* __restrict__ nbr, int* __restrict__ cnt_out, int* __restrict__ indeg) {
+                 int* __restrict__ nbr, int* __restrict__ cnt_out, int* __restrict__ indeg,
+                 int* __restrict__ tail_ticket, int* __restrict__ edge_ptr, int* __restrict__ n_edges,
+                 int* __restrict__ recv_ptr) {
   pdl_wait();                                 // programmatic dependent launch: see common.cuh
   pdl_launch_dependents();
   __shared__ double s_bd[kNbrWarps][kNbrBuf];
   __shared__ int s_bj[kNbrWarps][kNbrBuf];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int q = blockIdx.x * kNbrWarps + w;  // query in cell-sorted order (neighbouring warps share cells)
-  if (q >= n) return;
+  if (q < n) {
   const GridParams gp = *gpp;
   double* bd = s_bd[w];
   int* bj = s_bj[w];
@@ -301,6 +421,9 @@ neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
   double sel_d[2];
   int sel_j[2];
   int count = 0;
+  // admission bound: r^2 until K candidates have been selected once, then the K-th smallest distance so far -- a
+  // candidate farther than K known ones can never make the list (ties at the bound stay in and are resolved by index)
+  double bound = r2;
   float4 nxt = fetch(lane);
   for (int f0 = 0; f0 < total; f0 += 32) {
     const float4 o = nxt;
@@ -308,7 +431,7 @@ neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
     const bool valid = f0 + lane < total;
     const double dx = px - (double)o.x, dyy = py - (double)o.y, dzz = pz - (double)o.z;
     const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dyy, dyy)), __dmul_rn(dzz, dzz));
-    const bool in = valid && d2 <= r2;
+    const bool in = valid && d2 <= bound;
     const unsigned m = __ballot_sync(0xffffffffu, in);
     if (in) {
       const int at = count + __popc(m & ((1u << lane) - 1u));
@@ -326,6 +449,7 @@ neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
         if (e < kept) { bd[e] = sel_d[i]; bj[e] = sel_j[i]; }
       }
       count = kept;
+      if (kept == K) bound = __shfl_sync(0xffffffffu, sel_d[(K - 1) >> 5], (K - 1) & 31);
       __syncwarp();
     }
   }
@@ -340,6 +464,46 @@ neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
     }
   }
   if (lane == 0) cnt_out[qi] = kept;
+  }
+  // tiny inputs: the last block to finish turns the out-degrees and in-degrees into edge_ptr / recv_ptr itself
+  // (replaces two single-block scan launches; tail_ticket == nullptr switches it off)
+  if (tail_ticket == nullptr) return;
+  __shared__ int s_last;
+  __shared__ int s_scan[9];
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(tail_ticket, 1) == (int)gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+#pragma unroll 1
+  for (int which = 0; which < 2; ++which) {
+    const int* in = which == 0 ? cnt_out : indeg;
+    int* out = which == 0 ? edge_ptr : recv_ptr;
+    int carry = 0;
+    for (int base0 = 0; base0 < n; base0 += kScanTile) {
+      const int base = base0 + (int)threadIdx.x * kScanItems;
+      int v[kScanItems], sum = 0;
+#pragma unroll
+      for (int i = 0; i < kScanItems; ++i) {
+        v[i] = base + i < n ? __ldcg(in + base + i) : 0;
+        sum += v[i];
+      }
+      int total;
+      int ex = block_exclusive_scan_256(sum, &total, s_scan) + carry;
+#pragma unroll
+      for (int i = 0; i < kScanItems; ++i) {
+        if (base + i < n) out[base + i] = ex;
+        ex += v[i];
+      }
+      carry += total;
+    }
+    if (threadIdx.x == 0) {
+      out[n] = carry;
+      if (which == 0) *n_edges = carry;
+    }
+    __syncthreads();
+  }
 }
 
 // ---- receiver CSR over "edge slots" (slot -> receiver, -1 = empty slot) ----
@@ -419,6 +583,39 @@ recv_sort_emit_warp_kernel(const int* __restrict__ recv_ptr, int n, const int* _
   }
 }
 
+// tiny inputs: out-degrees -> edge_ptr (+ n_edges) and in-degrees -> recv_ptr in ONE launch of two blocks
+__global__ void __launch_bounds__(kScanThreads)
+scan_degrees_kernel(const int* __restrict__ cnt, const int* __restrict__ indeg, int n, int* __restrict__ edge_ptr,
+                    int* __restrict__ n_edges, int* __restrict__ recv_ptr) {
+  pdl_wait();                                 // programmatic dependent launch: see common.cuh
+  pdl_launch_dependents();
+  __shared__ int s_scan[9];
+  const int* in = blockIdx.x == 0 ? cnt : indeg;
+  int* out = blockIdx.x == 0 ? edge_ptr : recv_ptr;
+  int carry = 0;
+  for (int base0 = 0; base0 < n; base0 += kScanTile) {
+    const int base = base0 + (int)threadIdx.x * kScanItems;
+    int v[kScanItems], sum = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      v[i] = base + i < n ? in[base + i] : 0;
+      sum += v[i];
+    }
+    int total;
+    int ex = block_exclusive_scan_256(sum, &total, s_scan) + carry;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      if (base + i < n) out[base + i] = ex;
+      ex += v[i];
+    }
+    carry += total;
+  }
+  if (threadIdx.x == 0) {
+    out[n] = carry;
+    if (blockIdx.x == 0) *n_edges = carry;
+  }
+}
+
 __global__ void copy_last_kernel(const int* __restrict__ ptr, int n, int* __restrict__ out) {
   if (threadIdx.x == 0 && blockIdx.x == 0) *out = ptr[n];
 }
@@ -458,7 +655,7 @@ void radius_graph_carve(Arena& a, int n_total, int /*n_graphs*/, int K, RadiusGr
 int build_recv_csr(const int* recv_of_slot, long long n_slots, const int* n_valid_dev, int n_nodes, int K,
                    const int* edge_ptr, const int* send_of_slot, int* indeg, int* fill, int* keys, int* scan_ws,
                    bool indeg_ready, int* recv_ptr, int* esend, int* erecv, int* eref, cudaStream_t stream,
-                   bool fill_ready) {
+                   bool fill_ready, bool recv_ptr_ready) {
   const int T = 256;
   if (!indeg_ready) {
     GM_CUDA(cudaMemsetAsync(indeg, 0, sizeof(int) * ((size_t)n_nodes + 1), stream));
@@ -468,8 +665,10 @@ int build_recv_csr(const int* recv_of_slot, long long n_slots, const int* n_vali
     }
   }
   if (!fill_ready) GM_CUDA(cudaMemsetAsync(fill, 0, sizeof(int) * ((size_t)n_nodes + 1), stream));
-  int rc = exclusive_scan_i32(indeg, recv_ptr, n_nodes, scan_ws, stream);
-  if (rc) return rc;
+  if (!recv_ptr_ready) {
+    int rc = exclusive_scan_i32(indeg, recv_ptr, n_nodes, scan_ws, stream);
+    if (rc) return rc;
+  }
   if (n_slots > 0) {
     GM_CUDA(launch_pdl(recv_fill_kernel, (int)ceil_div(n_slots, T), T, 0, stream, 1, recv_of_slot, n_slots, n_valid_dev, recv_ptr,
                        fill, keys));
@@ -498,7 +697,27 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
   GridParams* gp = reinterpret_cast<GridParams*>(ws.grid);
 
   const bool small = n <= kSmallN;
+  static const bool tiny_off = [] { const char* e = getenv("GM_GRAPH_TINY"); return e && e[0] == '0'; }();   // A/B aid
+  const bool tiny = n <= kTinyN && kNbrWarps * 32 == kScanThreads && !tiny_off;
   GM_PROF(kProfGrid);
+  if (tiny) {
+    // one block builds the cell list, one launch scans both degree arrays: 5 launches for the whole graph
+    int* ticket = reinterpret_cast<int*>(ws.bbox) + 7;
+    GM_CUDA(launch_pdl(cell_list_tiny_kernel, 1, kTinyThreads, 0, stream, 1, pos, pos_stride, n, n_per_graph, r, n_graphs,
+                       ws.max_cells, gp,
+                       ws.cell_start, ws.sorted, ws.indeg, ticket));
+    GM_PROF(kProfNeighbour);
+    GM_CUDA(launch_pdl(neighbour_kernel, ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream, 1, ws.sorted, ws.cell_start, gp, n,
+                       n_per_graph, r * r, K, nbr, cnt, ws.indeg, (int*)nullptr, (int*)nullptr, (int*)nullptr, (int*)nullptr));
+    GM_PROF(kProfCsr);
+    GM_CUDA(launch_pdl(scan_degrees_kernel, 2, kScanThreads, 0, stream, 1, (const int*)cnt, (const int*)ws.indeg, n, edge_ptr,
+                       n_edges, recv_ptr));
+    GM_LAUNCHED(3);
+    GM_LAUNCH_CHECK("radius_graph kernels (tiny path)");
+    return build_recv_csr(nbr, (long long)n * K, nullptr, n, K, edge_ptr, nullptr, ws.indeg, ws.fill, ws.keys, ws.scan_ws,
+                          /*indeg_ready=*/true, recv_ptr, esend, erecv, eref, stream, /*fill_ready=*/true,
+                          /*recv_ptr_ready=*/true);
+  }
   if (small) {
     GM_CUDA(launch_pdl(prepare_small_kernel, 1, 1024, 0, stream, 1, pos, pos_stride, n, r, n_graphs, ws.max_cells, gp, ws.cell_cnt,
                        ws.indeg));
@@ -521,14 +740,14 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
                      ws.cell_cnt, ws.sorted));
   GM_PROF(kProfNeighbour);
   GM_CUDA(launch_pdl(neighbour_kernel, ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream, 1, ws.sorted, ws.cell_start, gp, n,
-                     n_per_graph, r * r, K, nbr, cnt, ws.indeg));
+                     n_per_graph, r * r, K, nbr, cnt, ws.indeg, (int*)nullptr, (int*)nullptr, (int*)nullptr, (int*)nullptr));
   GM_LAUNCHED(3);
   GM_LAUNCH_CHECK("radius_graph kernels");
   GM_PROF(kProfCsr);
   rc = exclusive_scan_i32(cnt, edge_ptr, n, ws.scan_ws, stream, n_edges);
   if (rc) return rc;
   return build_recv_csr(nbr, (long long)n * K, nullptr, n, K, edge_ptr, nullptr, ws.indeg, ws.fill, ws.keys,
-                        ws.scan_ws, /*indeg_ready=*/true, recv_ptr, esend, erecv, eref, stream, /*fill_ready=*/small);
+                        ws.scan_ws, /*indeg_ready=*/true, recv_ptr, esend, erecv, eref, stream, /*fill_ready=*/small, false);
 }
 
 GM_TRACE_DUMP(trace_dump_radius)

@@ -31,6 +31,6 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
 int build_recv_csr(const int* recv_of_slot, long long n_slots, const int* n_valid_dev, int n_nodes, int K,
                    const int* edge_ptr, const int* send_of_slot, int* indeg, int* fill, int* keys, int* scan_ws,
                    bool indeg_ready, int* recv_ptr, int* esend, int* erecv, int* eref, cudaStream_t stream,
-                   bool fill_ready = false);
+                   bool fill_ready = false, bool recv_ptr_ready = false);
 
 }  // namespace gm

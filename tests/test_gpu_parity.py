@@ -124,6 +124,25 @@ def test_graph_batched_graphs_are_independent(gm, oracle_lib):
     assert torch.equal(ei[0], torch.cat(s_ref)) and torch.equal(ei[1], torch.cat(r_ref))
 
 
+def test_graph_cell_budget_of_the_single_block_path(gm, oracle_lib):
+    """Inputs of at most 8 192 particles build their cell list in one block with shared-memory counters; the grid must
+    then fit BOTH those counters and the caller's cell_start buffer (4 n + 2 entries).  5 graphs x 400 particles whose
+    joint bounding box gives 13 x 14 x 9 = 1 638 cells per graph = 8 190 cells in total (> 4 n = 8 000): the cell edge
+    has to grow.  (A rollout whose rigid particles are flung far away produced exactly this and read past cell_start.)"""
+    n, G, r = 400, 5, scene.CONN_R
+    poss = [scene.lattice_positions(n, 0.005, seed=60 + i, origin=0.32)[0] for i in range(G)]
+    poss[0][0] = torch.tensor([0.30, 0.30, 0.30])
+    poss[0][1] = torch.tensor([0.30 + 12.5 * r, 0.30 + 13.5 * r, 0.30 + 8.5 * r])
+    g = gm.radius_graph(torch.cat(poss), r, 20, n_graphs=G)
+    ei = g.edge_index().cpu()
+    s_ref, r_ref = [], []
+    for i, p in enumerate(poss):
+        s, rr = oracle_lib.get_connectivity(p, r, 20)
+        s_ref.append(s + n * i)
+        r_ref.append(rr + n * i)
+    assert torch.equal(ei[0], torch.cat(s_ref)) and torch.equal(ei[1], torch.cat(r_ref))
+
+
 def test_graph_full_size_properties(gm, oracle_lib):
     """C3 size (100k particles): size-independent properties + the C oracle (seconds on one core)."""
     n, K = 100_000, 20
