@@ -277,7 +277,7 @@ def tensor_roofline(ms_edge, E, pk):
     """mp_edge_kernel timed ALONE with CUDA events -> burst bf16 peak is the denominator; the sustained figure beside."""
     tf = FLOP_PER_EDGE_MP * E / (ms_edge * 1e-3) / 1e12
     gbs = BYTES_PER_EDGE_MP * E / (ms_edge * 1e-3) / 1e9
-    return {"kernel": "mp_edge_kernel", "bound": "tensor", "achieved": tf, "peak": pk["tf_burst"], "unit": "TFLOP/s",
+    return {"kernel": "mp_edge16_kernel", "bound": "tensor", "achieved": tf, "peak": pk["tf_burst"], "unit": "TFLOP/s",
             "frac": tf / pk["tf_burst"], "traffic": None, "peak_source": pk["source"] + " burst (kernel timed alone)",
             "frac_of_sustained_peak": tf / pk["tf_sust"],
             "executed_frac": 1.8 * tf / pk["tf_burst"],   # bf16x3: 3 x 98 304 MAC-flops executed per 163 840 algorithmic

@@ -736,6 +736,489 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
 }
 
 // ================================================================================================
+// mp_edge16_kernel: the same CTA-pair pipeline (memory plan, MMAs, barriers, fp32 order of the segmented sum) with
+// EIGHT warps per 128-edge tile -- 544 threads per CTA: warps 0-7 slot 0, warps 8-15 slot 1, warp 16 the MMA issuer.
+// Thread = edge row x two of the four 32-column boxes (warp w: rows 32 (w & 3) .., boxes h and h + 2 with
+// h = (w >> 2) & 1, so every warp contributes to both K halves of the next operand and a K half is complete after
+// ONE box of epilogue work per thread).  Sixteen compute warps at <= 120 registers (a thread holds 64 columns, not
+// 128) instead of eight at 232: four warps per scheduler hide the latencies (tcgen05.ld, shared memory, L1 / L2)
+// that bound the 8-warp kernel (ncu: issue slots 35 %, tensor pipe 33 %, nothing saturated), and the chain of a tile
+// is half as long.  LayerNorm statistics of a row are combined from the two half rows (sum and centred sum of
+// squares, exchanged through the row's own staging bytes); staging, residual reductions and the segment stores stay
+// warp-local (a warp moves its own rows x its own boxes), the segmented sweep is thread = column x 64-row block.
+// ================================================================================================
+namespace {
+constexpr int kNTE16 = 640;                  // 16 compute warps + the issuer's warpgroup (warp 16 issues, 17-19 idle)
+constexpr int kIssuerWarp16 = 16;
+
+// lane l of warp (q, h) moves float4 j16 of row r0 + 2 i + (l >> 4) in instruction i (16 instructions per 32 rows);
+// float4 index in the row: box h + 2 ((l >> 3) & 1), chunk l & 7
+__device__ __forceinline__ int stage16_j(int lane, int h) { return (h + 2 * ((lane >> 3) & 1)) * 8 + (lane & 7); }
+// staging-tile offset of this lane's float4 of row r0 + 2 i + sub: (row & 7) = (2 i + sub) & 7 because r0 % 8 == 0
+__device__ __forceinline__ uint32_t stage16_off(uint32_t db_base, uint32_t db_x, int i) {
+  return db_base + (uint32_t)i * 256u + (db_x ^ (((uint32_t)i & 3u) << 5));
+}
+__device__ __forceinline__ void stage16_contig(uint32_t S_s, uint32_t db_base, uint32_t db_x, const float* src0,
+                                               int n_valid, int sub) {
+  if (n_valid >= 32) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) cp_async16(S_s + stage16_off(db_base, db_x, i), src0 + 2 * i * kH, 16u);
+  } else {
+#pragma unroll 4
+    for (int i = 0; i < 16; ++i) {
+      const bool ok = 2 * i + sub < n_valid;
+      cp_async16(S_s + stage16_off(db_base, db_x, i), ok ? src0 + 2 * i * kH : src0, ok ? 16u : 0u);
+    }
+  }
+  cp_async_commit();
+}
+__device__ __forceinline__ void stage16_gather(uint32_t S_s, uint32_t db_base, uint32_t db_x, const float* table_j,
+                                               int my_idx, int sub) {
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int sid = __shfl_sync(0xffffffffu, my_idx, 2 * i + sub);
+    cp_async16(S_s + stage16_off(db_base, db_x, i), table_j + (size_t)(sid < 0 ? 0 : sid) * kH, sid < 0 ? 0u : 16u);
+  }
+  cp_async_commit();
+}
+}  // namespace
+
+__global__ void __launch_bounds__(kNTE16, 1) mp_edge16_kernel(TcMlp m, TcGraph g, TcBuffers b) {
+  extern __shared__ __align__(1024) char smem_raw[];
+  char* base = smem_raw;
+  const uint32_t W_s = smem_u32(base);
+  char* S_base = base + kWBytes;
+  EdgeShared* sh = reinterpret_cast<EdgeShared*>(S_base + 2 * kStageBytes);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = cluster_ctarank();     // 0: leader (issues the pair's MMAs), 1: peer
+  if (tid == 0 && (W_s & 1023u) != 0u) {
+    printf("gnn_manip_b200: mp_edge16 dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+  if (tid == 0) {
+    mbar_init(smem_u32(&sh->w_full), 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(smem_u32(&sh->a_half[s][0]), 16);   // 8 warps of the slot in each CTA of the pair
+      mbar_init(smem_u32(&sh->a_half[s][1]), 16);
+      mbar_init(smem_u32(&sh->d_ready[s]), 1);
+    }
+    fence_mbar_init();
+    mbar_expect_tx(smem_u32(&sh->w_full), kWBytes);
+    for (int l = 0; l < 3; ++l)
+      for (int p = 0; p < 4; ++p)
+        bulk_g2s(W_s + l * kWLayer + p * kWBlock, (const char*)m.wc[l] + (size_t)p * kPieceBytes + rank * kWBlock,
+                 kWBlock, smem_u32(&sh->w_full));
+  }
+  if (warp == 0) tmem_alloc_pair(smem_u32(&sh->tmem_base), 512);
+  for (int i = tid; i < kH; i += kNTE16) {
+    sh->prm[kOffB2 + i] = m.b2[i];
+    sh->prm[kOffB3 + i] = m.b3[i];
+    sh->prm[kOffG + i] = m.ln_g[i];
+    sh->prm[kOffBeta + i] = m.ln_b[i];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sh->tmem_base;
+                                 // everything above touched constant parameters only
+
+  const int E = min(*g.n_edges_dev, g.max_edges);
+  const int n_tiles = (E + kTile - 1) / kTile;
+  const int grid = (int)gridDim.x;
+  const int b_lead = (int)blockIdx.x - (int)rank;
+  const int n_my = b_lead < n_tiles ? (n_tiles - b_lead + grid - 1) / grid : 0;
+  if (warp >= kIssuerWarp16) {
+    // ---------------- fifth warpgroup: hands its registers to the compute warps (a scheduler holds four compute warps
+    //                  and one warp of this group: 4 x 120 + 24 registers per lane); lane 0 of warp 16 in the leader
+    //                  CTA issues every MMA: items of a slot in order (tile, layer, K half) ----------------
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    mbar_wait(smem_u32(&sh->w_full), 0);
+    cluster_sync_all();                        // pairs with the compute warps' prologue barrier
+    if (warp == kIssuerWarp16 && lane == 0 && rank == 0) {
+      int it[2] = {0, 0};
+      const int end[2] = {6 * ((n_my + 1) / 2), 6 * (n_my / 2)};
+      uint32_t idle = 0;
+      while (it[0] < end[0] || it[1] < end[1]) {
+        bool progress = false;
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          if (it[s] < end[s]) {
+            const int half = it[s] & 1, layer = (it[s] >> 1) % 3;
+            if (mbar_try_wait(smem_u32(&sh->a_half[s][half]), (uint32_t)(it[s] >> 1) & 1u)) {
+              tc_fence_after();
+              const uint32_t tXs = tmem + 256u * s, tYs = tXs + 128u;
+              issue_half_pair(W_s + layer * kWLayer, layer == 1 ? tXs : tYs, layer == 1 ? tYs : tXs, half);
+              if (half) umma_commit_pair(smem_u32(&sh->d_ready[s]));
+              ++it[s];
+              progress = true;
+            }
+          }
+        }
+        if (progress) idle = 0;
+        else if (++idle > (1u << 28)) {
+          printf("gnn_manip_b200: mp_edge16 issuer timed out (block %d)\n", blockIdx.x);
+          __trap();
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---------------- compute warps: slot s, thread = edge row r x boxes {h, h + 2} ----------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+    const int s = warp >> 3, q = warp & 3, h = (warp >> 2) & 1, r0 = q * 32, r = r0 + lane, sub = lane >> 4;
+    const int c0 = h, c1 = h + 2;              // this thread's 32-column boxes: K half 0 and K half 1 of an operand
+    const int KSTEP = 2, K0 = s;               // slot s takes this CTA's tiles s, s + 2, ...
+    const int bar_slot = 1 + s, bar_rowpair = 3 + 4 * s + q;   // named barriers: the slot (256), the two warps of a row (64)
+    char* S = S_base + s * kStageBytes;
+    const uint32_t S_s = smem_u32(S);
+    // row-owner offset of chunk j of a box: r * 128 + ((j ^ (r & 7)) << 4), rematerialised (one LOP3) at every use
+    const uint32_t ro_base = (uint32_t)r * 128u, ro_x = ((uint32_t)r & 7u) << 4;
+#define RO16(j) (ro_base | (ro_x ^ ((uint32_t)(j) << 4)))
+    // regions of this slot: layer 1 reads X and accumulates into Y, layer 2 reads Y -> X, layer 3 reads X -> Y
+    const uint32_t tX = tmem + 256u * s + ((uint32_t)r0 << 16), tY = tX + 128u;   // this warp's lanes
+    const uint32_t bar_d = smem_u32(&sh->d_ready[s]);
+    const uint32_t bar_a0 = mapa_shared(smem_u32(&sh->a_half[s][0]), 0);           // leader CTA's
+    const uint32_t bar_a1 = mapa_shared(smem_u32(&sh->a_half[s][1]), 0);
+    const float* prm = sh->prm;
+    auto publish_half = [&](int half) {        // this warp's box of K half `half` of the next operand is in TMEM
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(half ? bar_a1 : bar_a0);
+    };
+    auto publish_both = [&]() {
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive_cluster(bar_a0);
+        mbar_arrive_cluster(bar_a1);
+      }
+    };
+    // ids of this thread's row in the slot's next tile; nx_send carries "this row starts a receiver segment" in bit 30
+    // (an invalid row is -1 / -1: flag set, like the 4-warp kernel's -1 != -2)
+    int nx_recv = -1, nx_send = -1;
+    auto fetch_ids = [&](int k) {
+      const int ge = (blockIdx.x + k * grid) * kTile + r;
+      nx_recv = nx_send = -1;
+      if (ge < E) {
+        nx_recv = __ldg(g.erecv + ge);
+        const int prev = ge > 0 ? __ldg(g.erecv + ge - 1) : -2;
+        nx_send = __ldg(g.esend + ge) | (nx_recv != prev ? 1 << 30 : 0);
+      }
+    };
+    // stager destination of this lane's float4 of row r0 + 2 i + sub: rematerialised, see stage16_off
+    const int j16 = stage16_j(lane, h);
+    const uint32_t db_base = (uint32_t)(j16 >> 3) * kBoxBytes + (uint32_t)(r0 + sub) * 128u;
+    const uint32_t db_x = (((uint32_t)j16 & 7u) ^ (uint32_t)sub) << 4;
+#define DB16(i) (db_base + (uint32_t)(i) * 256u + (db_x ^ (((uint32_t)(i) & 3u) << 5)))
+    auto stage_e_rows = [&](int k) {           // this warp's 32 rows x 2 boxes of tile k
+      const int ge0 = (blockIdx.x + k * grid) * kTile + r0;
+      stage16_contig(S_s, db_base, db_x, b.e + (size_t)(ge0 + sub < E ? ge0 + sub : 0) * kH + 4 * j16, E - ge0, sub);
+    };
+    int cur_recv = -1;
+    auto box_to_operand = [&](int c, uint32_t tR) {
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 t = *reinterpret_cast<const float4*>(S + c * kBoxBytes + RO16(j));
+        v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+      }
+      put_operand32_inplace(v, tR, c);
+    };
+    // e rows of a tile (landed in this warp's staging bytes) -> bf16 hi / lo operand of layer 1 in TMEM
+    auto operand_from_stage = [&]() {
+      cp_async_wait_all();
+      __syncwarp();
+      box_to_operand(c0, tX);
+      box_to_operand(c1, tX);
+      tmem_st_wait();
+      __syncwarp();                            // every lane is done reading this warp's staging bytes
+    };
+    auto begin_tile = [&]() {
+      cur_recv = nx_recv;
+      {
+        const unsigned mk = __ballot_sync(0xffffffffu, (nx_send >> 30) & 1);
+        if (lane == 0 && h == 0) sh->segmask[s][q] = mk;
+      }
+      const float* pr_row = b.pr + (size_t)max(cur_recv, 0) * kH;
+      prefetch_l1(pr_row + 32 * c0);
+      prefetch_l1(pr_row + 32 * c1);
+      stage16_gather(S_s, db_base, db_x, b.ps + 4 * j16, nx_send < 0 ? -1 : (nx_send & 0x3fffffff), sub);
+    };
+    if (K0 < n_my) {
+      fetch_ids(K0);
+      stage_e_rows(K0);
+    }
+    // weights of this CTA landed; peer barriers initialised, peer weights landed, TMEM of the pair allocated
+    mbar_wait(smem_u32(&sh->w_full), 0);
+    cluster_sync_all();
+    if (K0 < n_my) {
+      operand_from_stage();
+      publish_both();                            // layer 1 of the first tile needs e and weights only: its GEMM runs
+                                                 // before the dependency wait as well
+    }
+    // Everything so far read only constants and e (written by the kernel two launches back); Pr / Ps come from the
+    // node kernel right before.
+    pdl_wait();
+    pdl_launch_dependents();
+    if (K0 < n_my) begin_tile();
+    for (int k = K0; k < n_my; k += KSTEP) {
+      const int row0 = (blockIdx.x + k * grid) * kTile;
+      const int rows_valid = min(kTile, E - row0);
+      const bool has_next = k + KSTEP < n_my;
+#ifdef GM_STAMPS
+      const bool stamp_on = blockIdx.x == 0 && tid == GM_STAMP_TID && k == 4;
+#endif
+      GM_ESTAMP(0);                              // stamps 0..14 in program order (tools_stamps.py, -DGM_STAMPS)
+      if (has_next) fetch_ids(k + KSTEP);
+      const uint32_t pt = (uint32_t)((k - K0) >> 1) & 1u;   // d_ready is used three times per tile: parities pt, pt ^ 1, pt
+      const float* pr_row = b.pr + (size_t)max(cur_recv, 0) * kH;
+      // ---- layer 1 epilogue: relu(D + Pr[recv] (b1 folded in) + Ps[send]) ----
+      cp_async_wait_all();
+      __syncwarp();
+      GM_ESTAMP(1);
+      mbar_wait(bar_d, pt);
+      tc_fence_after();
+      GM_ESTAMP(2);
+      {
+        float va[32];
+        float4 p[8];
+        auto load_pr = [&](int c) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) p[j] = __ldg(reinterpret_cast<const float4*>(pr_row + c * 32) + j);
+        };
+        auto e1_block = [&](int c, float* v) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 s4 = *reinterpret_cast<const float4*>(S + c * kBoxBytes + RO16(j));
+            v[4 * j] = fmaxf(v[4 * j] + (p[j].x + s4.x), 0.f);
+            v[4 * j + 1] = fmaxf(v[4 * j + 1] + (p[j].y + s4.y), 0.f);
+            v[4 * j + 2] = fmaxf(v[4 * j + 2] + (p[j].z + s4.z), 0.f);
+            v[4 * j + 3] = fmaxf(v[4 * j + 3] + (p[j].w + s4.w), 0.f);
+          }
+          put_operand32_inplace(v, tY, c);
+        };
+        tmem_ld32(tY + 32 * c0, va);
+        load_pr(c0);
+        tmem_ld_wait();
+        e1_block(c0, va);
+        tmem_ld32(tY + 32 * c1, va);
+        load_pr(c1);
+        publish_half(0);
+        tmem_ld_wait();
+        e1_block(c1, va);
+      }
+      publish_half(1);
+      GM_ESTAMP(3);
+      // this warp's staging bytes are free until its LayerNorm rows go in: the e rows of the slot's next tile land
+      // here while layers 2 and 3 run
+      if (has_next) stage_e_rows(k + KSTEP);
+      // ---- layer 2 epilogue: relu(D + b2) ----
+      mbar_wait(bar_d, pt ^ 1u);
+      tc_fence_after();
+      GM_ESTAMP(4);
+      {
+        float va[32];
+        auto e2_block = [&](int c, float* v) {
+          float4 bs[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bs[j] = GM_PRM4(prm + kOffB2 + c * 32 + 4 * j);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            v[4 * j] = fmaxf(v[4 * j] + bs[j].x, 0.f);
+            v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs[j].y, 0.f);
+            v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs[j].z, 0.f);
+            v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs[j].w, 0.f);
+          }
+          put_operand32_inplace(v, tX, c);
+        };
+        tmem_ld32(tX + 32 * c0, va);
+        tmem_ld_wait();
+        e2_block(c0, va);
+        tmem_ld32(tX + 32 * c1, va);
+        publish_half(0);
+        tmem_ld_wait();
+        e2_block(c1, va);
+      }
+      publish_half(1);
+      GM_ESTAMP(5);
+      // ---- layer 3 epilogue: y = LayerNorm(D + b3) -> this thread's staging bytes ----
+      mbar_wait(bar_d, pt);
+      tc_fence_after();
+      GM_ESTAMP(6);
+      if (has_next) operand_from_stage();
+      GM_ESTAMP(7);      // the A region is free (GEMM 3 is complete); D is read right below
+      {
+        // Two passes over the accumulator (tcgen05.ld twice; 32 live values instead of 64 keeps the kernel free of
+        // spills at 120 registers).  Pass 1: per 32-column box an exact two-pass (sum, centred sum of squares), the
+        // two boxes and then the two half rows combined like a two-pass variance (Chan et al.):
+        // M2 = M2_a + M2_b + n_a (mean_a - mean)^2 + n_b (mean_b - mean)^2.
+        float sum_h = 0.f, m2_h = 0.f, mean_c0 = 0.f;
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c = cc ? c1 : c0;
+          float x[32];
+          tmem_ld32(tY + 32 * c, x);
+          float4 t[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) t[j] = GM_PRM4(prm + kOffB3 + c * 32 + 4 * j);
+          tmem_ld_wait();
+          float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            x[4 * j] += t[j].x; x[4 * j + 1] += t[j].y; x[4 * j + 2] += t[j].z; x[4 * j + 3] += t[j].w;
+            sa += x[4 * j]; sb += x[4 * j + 1]; sc += x[4 * j + 2]; sd += x[4 * j + 3];
+          }
+          const float sum_c = (sa + sb) + (sc + sd), mean_c = sum_c * (1.0f / 32.0f);
+          float qa = 0.f, qb = 0.f, qc = 0.f, qd = 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float u0 = x[4 * j] - mean_c, u1 = x[4 * j + 1] - mean_c, u2 = x[4 * j + 2] - mean_c, u3 = x[4 * j + 3] - mean_c;
+            qa = fmaf(u0, u0, qa); qb = fmaf(u1, u1, qb); qc = fmaf(u2, u2, qc); qd = fmaf(u3, u3, qd);
+          }
+          const float m2_c = (qa + qb) + (qc + qd);
+          if (cc == 0) {
+            sum_h = sum_c; m2_h = m2_c; mean_c0 = mean_c;
+          } else {
+            const float dm = mean_c - mean_c0;
+            sum_h += sum_c;
+            m2_h = (m2_h + m2_c) + 16.0f * (dm * dm);   // n_a n_b / (n_a + n_b) = 16
+          }
+        }
+        // exchange with the thread that owns the other two boxes of this row (warp w ^ 4): each side parks its pair
+        // in its own staging bytes (free: the e rows were consumed above), reads the other's between two barriers
+        GM_ESTAMP(8);
+        *reinterpret_cast<float2*>(S + c0 * kBoxBytes + RO16(0)) = make_float2(sum_h, m2_h);
+        named_bar_sync(bar_rowpair, 64);
+        const float2 other = *reinterpret_cast<const float2*>(S + (c0 ^ 1) * kBoxBytes + RO16(0));
+        named_bar_sync(bar_rowpair, 64);
+        GM_ESTAMP(9);
+        const float mean = (sum_h + other.x) * (1.0f / kH);
+        const float dm = (sum_h - other.x) * (1.0f / 64.0f);           // mean_h - mean_other
+        const float m2 = (m2_h + other.y) + 32.0f * (dm * dm);          // n_a n_b / (n_a + n_b) = 32
+        const float rstd = 1.0f / sqrtf(m2 * (1.0f / kH) + 1e-5f);
+        // Pass 2: normalise and park the row in this thread's staging bytes
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c = cc ? c1 : c0;
+          float x[32];
+          tmem_ld32(tY + 32 * c, x);
+          float4 t[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) t[j] = GM_PRM4(prm + kOffB3 + c * 32 + 4 * j);
+          tmem_ld_wait();
+          // the accumulator has been read for the last time and the next tile's layer-1 operand is in TMEM: its
+          // GEMM 1 runs under the residual / segmented-sum phases of this tile
+          if (cc == 1 && has_next) publish_both();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 g4 = GM_PRM4(prm + kOffG + c * 32 + 4 * j);
+            const float4 b4 = GM_PRM4(prm + kOffBeta + c * 32 + 4 * j);
+            *reinterpret_cast<float4*>(S + c * kBoxBytes + RO16(j)) =
+                make_float4(((x[4 * j] + t[j].x) - mean) * rstd * g4.x + b4.x,
+                            ((x[4 * j + 1] + t[j].y) - mean) * rstd * g4.y + b4.y,
+                            ((x[4 * j + 2] + t[j].z) - mean) * rstd * g4.z + b4.z,
+                            ((x[4 * j + 3] + t[j].w) - mean) * rstd * g4.w + b4.w);
+          }
+        }
+      }
+      __syncwarp();
+      GM_ESTAMP(10);
+      // ---- e' = e + y (epd_gnn.py:104): this warp's rows x boxes leave as vector reductions, the add happens in L2 ----
+      {
+        const int nr = min(32, rows_valid - r0);
+        float* e_out = b.e + (size_t)(row0 + r0 + sub) * kH + 4 * j16;
+        if (nr >= 32) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            red_add_v4(e_out + 2 * i * kH, *reinterpret_cast<const float4*>(S + DB16(i)));
+        } else {
+#pragma unroll 4
+          for (int i = 0; i < 16; ++i)
+            if (2 * i + sub < nr)
+              red_add_v4(e_out + 2 * i * kH, *reinterpret_cast<const float4*>(S + DB16(i)));
+        }
+      }
+      GM_ESTAMP(11);
+      named_bar_sync(bar_slot, 256);
+      GM_ESTAMP(12);
+      // ---- receiver-segmented sum of the pre-residual rows (scatter_sum, gn_utils.py:60-64): thread = column r of
+      //      64-row block h.  Sweep A: running sum along the rows, restarted at segment starts and written back in
+      //      place at segment ends (uniform bit masks, strictly sequential fp32 order).  Sweep B: one 512 B store per
+      //      segment end -> aggpart[receiver] (or carry[] for a segment that began before this 64-row block). ----
+      {
+        const uint32_t cbase = (uint32_t)(r >> 5) * kBoxBytes + ((uint32_t)r & 3u) * 4u;
+        const uint32_t cchunk = ((uint32_t)r >> 2) & 7u;
+        uint32_t co[8];
+#pragma unroll
+        for (int ii = 0; ii < 8; ++ii) co[ii] = cbase + ((cchunk ^ (uint32_t)ii) << 4);
+        const int n0 = max(0, min(kAggRows, rows_valid)), n1 = max(0, min(kAggRows, rows_valid - kAggRows));
+        const unsigned long long f0 = ((unsigned long long)sh->segmask[s][1] << 32) | sh->segmask[s][0];
+        const unsigned long long f1 = ((unsigned long long)sh->segmask[s][3] << 32) | sh->segmask[s][2];
+        const unsigned long long v0 = n0 >= 64 ? ~0ull : ((1ull << n0) - 1ull), v1 = n1 >= 64 ? ~0ull : ((1ull << n1) - 1ull);
+        const unsigned long long m0 = f0 & ~1ull & v0, m1 = f1 & ~1ull & v1;              // restart points
+        const unsigned long long e0 = ((m0 >> 1) | (n0 > 0 ? 1ull << (n0 - 1) : 0ull)) & v0;   // segment ends
+        const unsigned long long e1 = ((m1 >> 1) | (n1 > 0 ? 1ull << (n1 - 1) : 0ull)) & v1;
+        {
+          const unsigned long long mh = h ? m1 : m0, eh = h ? e1 : e0;
+          float a0 = 0.f;
+#pragma unroll 1
+          for (int bb = 0; bb < kAggRows / 8; ++bb) {
+            float y0[8];
+            char* p = S + h * (kAggRows * 128) + bb * 1024;
+#pragma unroll
+            for (int ii = 0; ii < 8; ++ii) y0[ii] = *reinterpret_cast<const float*>(p + co[ii] + ii * 128);
+            const unsigned sb0 = (unsigned)(mh >> (8 * bb)) & 0xffu, eb0 = (unsigned)(eh >> (8 * bb)) & 0xffu;
+            if ((sb0 | eb0) == 0u) {
+#pragma unroll
+              for (int ii = 0; ii < 8; ++ii) a0 += y0[ii];
+            } else {
+#pragma unroll
+              for (int ii = 0; ii < 8; ++ii) {
+                const float t = a0 + y0[ii];
+                a0 = ((sb0 >> ii) & 1u) ? y0[ii] : t;
+                if ((eb0 >> ii) & 1u) *reinterpret_cast<float*>(p + co[ii] + ii * 128) = a0;
+              }
+            }
+          }
+        }
+        named_bar_sync(bar_slot, 256);
+        {
+          // warp (q, h) owns the segment ends of rows 32 q + 16 h .. + 15 (64-row block q >> 1)
+          const unsigned long long eb = q < 2 ? e0 : e1, fb = q < 2 ? f0 : f1;
+          const int off = (q & 1) * 32 + 16 * h;
+          unsigned ends = (unsigned)(eb >> off) & 0xffffu;
+          // the first end of a 64-row block belongs to a segment that began in the previous block iff flag bit 0 is clear
+          const bool cont_first = !(fb & 1ull) && (eb & ((1ull << off) - 1ull)) == 0ull;
+          const size_t agg_tile = (size_t)row0 / kAggRows + (q >> 1);
+          bool first = true;
+          while (ends != 0u) {
+            const int i = 16 * h + __ffs((int)ends) - 1;
+            ends &= ends - 1u;
+            const int rid = __shfl_sync(0xffffffffu, cur_recv, i);
+            const float4 v = *reinterpret_cast<const float4*>(S + stage_chunk_off(r0 + i, lane));
+            float* dst = (first && cont_first) ? b.carry + agg_tile * kH : b.aggpart + (size_t)rid * kH;
+            *reinterpret_cast<float4*>(dst + 4 * lane) = v;
+            first = false;
+          }
+        }
+      }
+      GM_ESTAMP(13);
+      named_bar_sync(bar_slot, 256);           // every row has been read: the slot's staging tile is free
+      GM_ESTAMP(14);
+      if (has_next) begin_tile();
+      GM_ESTAMP(15);
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();                          // the peer may still be arriving on / reading through this CTA
+  if (warp == 0) tmem_dealloc_pair(tmem, 512);
+}
+#undef RO16
+#undef DB16
+
+// ================================================================================================
 // enc_edge (pair version): edge encoder of EncProcDecGNN.forward (epd_gnn.py:30-33,88) on the same CTA-pair
 // pipeline.  Edge features (row A2, utils.py:43-61) are built on the fly from positions; Linear(4,128)+ReLU runs
 // on CUDA cores straight into the TMEM operand, the two 128x128 layers on the tensor cores with both weight chunks
@@ -1036,6 +1519,7 @@ int tc_configure_edge() {
   if (dev == -1) return GM_OK;
   GM_REQUIRE(dev >= 0, "tc_configure_edge: cannot query the current device");
   GM_CUDA(cudaFuncSetAttribute(mp_edge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEdgeSmemBytes));
+  GM_CUDA(cudaFuncSetAttribute(mp_edge16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEdgeSmemBytes));
   GM_CUDA(cudaFuncSetAttribute(enc_edge_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kEdgeSmemBytes));
   GM_CUDA(cudaFuncSetAttribute(selftest_gemm_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSelftestTsSmem));
   once.finish(dev);
@@ -1050,7 +1534,13 @@ int tc_mp_edge(const TcMlp& m, const TcGraph& g, const TcBuffers& b, cudaStream_
   const int grid = min((ceil_div(g.max_edges, kTile) + 1) & ~1, kNumSMs & ~1);
   // programmatic = false: fully ordered after everything before it in the stream (its early part reads e, which
   // must then come from the kernel right before it or from a joined stream)
-  GM_CUDA(launch_ex(mp_edge_kernel, grid, kNTE3, (size_t)kEdgeSmemBytes, stream, 2, programmatic, m, g, b));
+  // default: eight warps per tile (mp_edge16_kernel); GM_EDGE_KERNEL=8 keeps the 4-warps-per-tile kernel for A/B runs
+  static const bool edge8 = [] { const char* e = getenv("GM_EDGE_KERNEL"); return e && e[0] == '8'; }();
+  if (edge8) {
+    GM_CUDA(launch_ex(mp_edge_kernel, grid, kNTE3, (size_t)kEdgeSmemBytes, stream, 2, programmatic, m, g, b));
+  } else {
+    GM_CUDA(launch_ex(mp_edge16_kernel, grid, kNTE16, (size_t)kEdgeSmemBytes, stream, 2, programmatic, m, g, b));
+  }
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("mp_edge_kernel");
   return GM_OK;

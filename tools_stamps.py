@@ -13,6 +13,9 @@ st = (ctypes.c_ulonglong * 64)()
 gm._lib.check(gm._lib.lib().gm_debug_stamps(st, 64), "gm_debug_stamps")
 s = np.array(st[:], dtype=np.int64)
 print("kernel ms", per, "E", E)
+names16 = ["top", "ps landed", "GEMM1 done", "E1 published", "GEMM2 done", "E2 published", "GEMM3 done", "next operand", "LN pass 1",
+           "LN exchange", "LN rows stored", "RED issued", "slot barrier", "sweeps done", "slot barrier", "next tile begun"]
+print("mp_edge16 (default edge kernel) phase deltas:", {names16[i + 1]: int(s[i + 1] - s[i]) for i in range(15)}, "tile:", int(s[15] - s[0]))
 print("edge compute stamps (cycles since stamp 0):", [int(x - s[0]) for x in s[:16]])
 print("edge compute deltas:", [int(s[i + 1] - s[i]) for i in range(15)])
 print("edge E1 fine stamps (since stamp 5: ld0 done, blk0, blk1, blk2, blk3, published, issued):", [int(x - s[5]) for x in s[16:23]])
