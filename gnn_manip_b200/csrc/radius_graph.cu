@@ -314,64 +314,86 @@ __global__ void cell_fill_kernel(const float* __restrict__ pos, int stride, int 
 }
 
 constexpr int kNbrWarps = 8;      // warps (queries) per block
-constexpr int kNbrBuf = 192;      // in-radius candidate buffer per warp
 constexpr int kMaxK = 64;
 
 __device__ __forceinline__ bool key_less(double da, int ja, double db, int jb) {
   return da < db || (da == db && ja < jb);
 }
 
-// The `keep` smallest (d2, j) keys of buf[0..cnt), cnt <= kNbrBuf, in ascending order: each lane holds up to
-// kNbrBuf / 32 candidates in registers; `keep` rounds of a warp-wide arg-min (keys are unique: j is).  Round r's
-// winner is returned in lane r % 32 (slot r / 32 of out_d / out_j).
-constexpr int kNbrPerLane = kNbrBuf / 32;
-__device__ __forceinline__ int warp_select_smallest(const double* bd, const int* bj, int cnt, int keep, int lane,
-                                                    double* out_d, int* out_j) {
-  double d[kNbrPerLane];
-  int j[kNbrPerLane];
+// Bitonic sort of 32 * PL (d2, j) keys held PL per lane (element e = slot * 32 + lane), ascending: afterwards the key of
+// rank r sits in lane r % 32, slot r / 32.  Keys are unique (j is), padding is (1e300, INT_MAX).  Exchanges at distance
+// >= 32 are register-local, the others one shuffle exchange per slot: 21 stages for PL = 2 (20 of them shuffled),
+// 28 for PL = 4 -- about a third of the instructions of K warp-wide arg-min rounds.
+template <int PL>
+__device__ __forceinline__ void warp_bitonic_sort(double (&d)[PL], int (&j)[PL], int lane) {
+  constexpr int kLog = PL == 2 ? 6 : 7;           // log2(32 * PL)
 #pragma unroll
-  for (int i = 0; i < kNbrPerLane; ++i) {
-    const int e = lane + 32 * i;
-    d[i] = e < cnt ? bd[e] : 1e300;
-    j[i] = e < cnt ? bj[e] : 0x7fffffff;
-  }
-  const int m = cnt < keep ? cnt : keep;
-  for (int r = 0; r < m; ++r) {
-    double bdv = d[0];
-    int bjv = j[0];
+  for (int lk = 1; lk <= kLog; ++lk) {
+    const int k = 1 << lk;
 #pragma unroll
-    for (int i = 1; i < kNbrPerLane; ++i)
-      if (key_less(d[i], j[i], bdv, bjv)) { bdv = d[i]; bjv = j[i]; }
+    for (int ls = kLog - 1; ls >= 0; --ls) {
+      if (ls >= lk) continue;                       // (fixed trip count so that both loops unroll completely)
+      const int st = 1 << ls;
+      if (st >= 32) {
+        const int ss = st >> 5;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const double od = __shfl_xor_sync(0xffffffffu, bdv, o);
-      const int oj = __shfl_xor_sync(0xffffffffu, bjv, o);
-      if (key_less(od, oj, bdv, bjv)) { bdv = od; bjv = oj; }
+        for (int s0 = 0; s0 < PL; ++s0) {
+          if ((s0 & ss) == 0) {
+            const int s1 = s0 | ss;
+            const bool asc = (((s0 << 5) & k) == 0);     // bit of e selected by k: slot bits only (k >= 64 here)
+            const bool lt = key_less(d[s1], j[s1], d[s0], j[s0]);
+            if (lt == asc) {
+              const double td = d[s0]; d[s0] = d[s1]; d[s1] = td;
+              const int tj = j[s0]; j[s0] = j[s1]; j[s1] = tj;
+            }
+          }
+        }
+      } else {
+#pragma unroll
+        for (int s0 = 0; s0 < PL; ++s0) {
+          const double od = __shfl_xor_sync(0xffffffffu, d[s0], st);
+          const int oj = __shfl_xor_sync(0xffffffffu, j[s0], st);
+          const int e = (s0 << 5) | lane;
+          const bool asc = (e & k) == 0, lower = (lane & st) == 0;
+          // the lower element of an ascending pair keeps the smaller key
+          const bool take = key_less(od, oj, d[s0], j[s0]) == (asc == lower);
+          if (take) { d[s0] = od; j[s0] = oj; }
+        }
+      }
     }
-#pragma unroll
-    for (int i = 0; i < kNbrPerLane; ++i)
-      if (j[i] == bjv) { d[i] = 1e300; j[i] = 0x7fffffff; }
-    if (lane == (r & 31)) {
-      if (r < 32) { out_d[0] = bdv; out_j[0] = bjv; }
-      else { out_d[1] = bdv; out_j[1] = bjv; }
-    }
   }
-  return m;
 }
 
+// buffer -> registers (padded with (1e300, INT_MAX)), sorted
+template <int PL>
+__device__ __forceinline__ void load_and_sort(const double* bd, const int* bj, int count, int lane, double (&kd)[PL],
+                                              int (&kj)[PL]) {
+#pragma unroll
+  for (int i = 0; i < PL; ++i) {
+    const int e = lane + 32 * i;
+    kd[i] = e < count ? bd[e] : 1e300;
+    kj[i] = e < count ? bj[e] : 0x7fffffff;
+  }
+  warp_bitonic_sort<PL>(kd, kj, lane);
+}
+
+// One warp per query (cell-sorted order).  Candidates within the admission bound are appended to a per-warp buffer of
+// 32 * PL keys; when the next 32 candidates might not fit, the buffer is sorted, its K smallest kept and the bound
+// lowered to the K-th smallest distance (a candidate farther than K known ones can never make the list; ties at
+// the bound stay in and are resolved by index).  PL = 2 serves K <= 32, PL = 4 K <= 64.
+template <int PL>
 __global__ void __launch_bounds__(kNbrWarps * 32)
 neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                  const GridParams* __restrict__ gpp, int n, int n_per_graph, double r2, int K,
-                 int* __restrict__ nbr, int* __restrict__ cnt_out, int* __restrict__ indeg,
-                 int* __restrict__ tail_ticket, int* __restrict__ edge_ptr, int* __restrict__ n_edges,
-                 int* __restrict__ recv_ptr) {
+                 int* __restrict__ nbr, int* __restrict__ cnt_out, int* __restrict__ indeg) {
   pdl_wait();                                 // programmatic dependent launch: see common.cuh
   pdl_launch_dependents();
-  __shared__ double s_bd[kNbrWarps][kNbrBuf];
-  __shared__ int s_bj[kNbrWarps][kNbrBuf];
+  constexpr int kBuf = 32 * PL;
+  __shared__ double s_bd[kNbrWarps][kBuf];
+  __shared__ int s_bj[kNbrWarps][kBuf];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int q = blockIdx.x * kNbrWarps + w;  // query in cell-sorted order (neighbouring warps share cells)
-  if (q < n) {
+  if (q >= n) return;
   const GridParams gp = *gpp;
   double* bd = s_bd[w];
   int* bj = s_bj[w];
@@ -417,12 +439,10 @@ neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
       if (f >= rx[t]) { sb = rb[t]; sx = rx[t]; }   // the last run whose prefix is <= f (empty runs are passed over)
     return sorted[sb + (f - sx)];
   };
+  double kd[PL];
+  int kj[PL];
 
-  double sel_d[2];
-  int sel_j[2];
   int count = 0;
-  // admission bound: r^2 until K candidates have been selected once, then the K-th smallest distance so far -- a
-  // candidate farther than K known ones can never make the list (ties at the bound stay in and are resolved by index)
   double bound = r2;
   float4 nxt = fetch(lane);
   for (int f0 = 0; f0 < total; f0 += 32) {
@@ -440,70 +460,52 @@ neighbour_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
     }
     count += __popc(m);
     __syncwarp();
-    if (count + 32 > kNbrBuf) {  // keep only the K best so far, then continue scanning
-      const int kept = warp_select_smallest(bd, bj, count, K, lane, sel_d, sel_j);
+    if (count + 32 > kBuf && f0 + 32 < total) {  // keep only the K best so far, then continue scanning
+      load_and_sort<PL>(bd, bj, count, lane, kd, kj);
+      const int kept = count < K ? count : K;
       __syncwarp();
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
+      for (int i = 0; i < PL; ++i) {
         const int e = lane + 32 * i;
-        if (e < kept) { bd[e] = sel_d[i]; bj[e] = sel_j[i]; }
+        if (e < kept) { bd[e] = kd[i]; bj[e] = kj[i]; }
       }
       count = kept;
-      if (kept == K) bound = __shfl_sync(0xffffffffu, sel_d[(K - 1) >> 5], (K - 1) & 31);
+      if (kept == K) {
+        // (every slot is shuffled and the right one selected afterwards: indexing kd[] with (K - 1) >> 5 would put the
+        // key registers into local memory)
+        double kth = __shfl_sync(0xffffffffu, kd[0], (K - 1) & 31);
+#pragma unroll
+        for (int i = 1; i < PL; ++i) {
+          const double t = __shfl_sync(0xffffffffu, kd[i], (K - 1) & 31);
+          kth = ((K - 1) >> 5) == i ? t : kth;
+        }
+        bound = kth;
+      }
       __syncwarp();
     }
   }
-  const int kept = warp_select_smallest(bd, bj, count, K, lane, sel_d, sel_j);
+  load_and_sort<PL>(bd, bj, count, lane, kd, kj);
+  const int kept = count < K ? count : K;
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < PL; ++i) {
     const int e = lane + 32 * i;
     if (e < K) {
-      const int j = e < kept ? sel_j[i] : -1;
+      const int j = e < kept ? kj[i] : -1;
       nbr[(size_t)qi * K + e] = j;
       if (j >= 0) atomicAdd(&indeg[j], 1);
     }
   }
   if (lane == 0) cnt_out[qi] = kept;
-  }
-  // tiny inputs: the last block to finish turns the out-degrees and in-degrees into edge_ptr / recv_ptr itself
-  // (replaces two single-block scan launches; tail_ticket == nullptr switches it off)
-  if (tail_ticket == nullptr) return;
-  __shared__ int s_last;
-  __shared__ int s_scan[9];
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) s_last = atomicAdd(tail_ticket, 1) == (int)gridDim.x - 1;
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-#pragma unroll 1
-  for (int which = 0; which < 2; ++which) {
-    const int* in = which == 0 ? cnt_out : indeg;
-    int* out = which == 0 ? edge_ptr : recv_ptr;
-    int carry = 0;
-    for (int base0 = 0; base0 < n; base0 += kScanTile) {
-      const int base = base0 + (int)threadIdx.x * kScanItems;
-      int v[kScanItems], sum = 0;
-#pragma unroll
-      for (int i = 0; i < kScanItems; ++i) {
-        v[i] = base + i < n ? __ldcg(in + base + i) : 0;
-        sum += v[i];
-      }
-      int total;
-      int ex = block_exclusive_scan_256(sum, &total, s_scan) + carry;
-#pragma unroll
-      for (int i = 0; i < kScanItems; ++i) {
-        if (base + i < n) out[base + i] = ex;
-        ex += v[i];
-      }
-      carry += total;
-    }
-    if (threadIdx.x == 0) {
-      out[n] = carry;
-      if (which == 0) *n_edges = carry;
-    }
-    __syncthreads();
-  }
+}
+
+// K <= 32 fits two keys per lane (buffer 64 >= K + 32), larger K four
+static cudaError_t launch_neighbour(cudaStream_t stream, const float4* sorted, const int* cell_start, const GridParams* gp,
+                                    int n, int n_per_graph, double r2, int K, int* nbr, int* cnt, int* indeg) {
+  if (K <= 32)
+    return launch_pdl(neighbour_kernel<2>, ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream, 1, sorted, cell_start, gp, n,
+                      n_per_graph, r2, K, nbr, cnt, indeg);
+  return launch_pdl(neighbour_kernel<4>, ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream, 1, sorted, cell_start, gp, n,
+                    n_per_graph, r2, K, nbr, cnt, indeg);
 }
 
 // ---- receiver CSR over "edge slots" (slot -> receiver, -1 = empty slot) ----
@@ -707,8 +709,7 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
                        ws.max_cells, gp,
                        ws.cell_start, ws.sorted, ws.indeg, ticket));
     GM_PROF(kProfNeighbour);
-    GM_CUDA(launch_pdl(neighbour_kernel, ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream, 1, ws.sorted, ws.cell_start, gp, n,
-                       n_per_graph, r * r, K, nbr, cnt, ws.indeg, (int*)nullptr, (int*)nullptr, (int*)nullptr, (int*)nullptr));
+    GM_CUDA(launch_neighbour(stream, ws.sorted, ws.cell_start, gp, n, n_per_graph, r * r, K, nbr, cnt, ws.indeg));
     GM_PROF(kProfCsr);
     GM_CUDA(launch_pdl(scan_degrees_kernel, 2, kScanThreads, 0, stream, 1, (const int*)cnt, (const int*)ws.indeg, n, edge_ptr,
                        n_edges, recv_ptr));
@@ -739,8 +740,7 @@ int radius_graph(const float* pos, int pos_stride, int n_per_graph, int n_graphs
   GM_CUDA(launch_pdl(cell_fill_kernel, ceil_div(n, T), T, 0, stream, 1, pos, pos_stride, n, ws.cell_of, ws.cell_start,
                      ws.cell_cnt, ws.sorted));
   GM_PROF(kProfNeighbour);
-  GM_CUDA(launch_pdl(neighbour_kernel, ceil_div(n, kNbrWarps), kNbrWarps * 32, 0, stream, 1, ws.sorted, ws.cell_start, gp, n,
-                     n_per_graph, r * r, K, nbr, cnt, ws.indeg, (int*)nullptr, (int*)nullptr, (int*)nullptr, (int*)nullptr));
+  GM_CUDA(launch_neighbour(stream, ws.sorted, ws.cell_start, gp, n, n_per_graph, r * r, K, nbr, cnt, ws.indeg));
   GM_LAUNCHED(3);
   GM_LAUNCH_CHECK("radius_graph kernels");
   GM_PROF(kProfCsr);
