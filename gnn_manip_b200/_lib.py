@@ -122,6 +122,7 @@ SIGNATURES = {
     "gm_train_layernorm_fwd": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_int32] + [c_void_p] * 6),
     "gm_train_layernorm_partial_bytes": (c_size_t, [c_int32]),
     "gm_train_layernorm_bwd": (ctypes.c_int, [c_void_p] * 6 + [c_int32] + [c_void_p] * 5),
+    "gm_train_layernorm_bwd_static": (ctypes.c_int, [c_void_p] * 6 + [c_int32] + [c_void_p] * 4),
     "gm_train_small_fwd": (ctypes.c_int, [c_void_p, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p,
                                           c_void_p]),
     "gm_train_small_partial_bytes": (c_size_t, [c_int32, c_int32, c_int32]),

@@ -948,6 +948,12 @@ int gm_train_layernorm_bwd(const float* d1, const float* d2, const int32_t* idx2
                    (cudaStream_t)stream);
 }
 
+int gm_train_layernorm_bwd_static(const float* d1, const float* d2, const int32_t* idx2, const float* xhat,
+                                  const float* rstd, const float* gamma, int32_t n_rows, float* dz, float* dgamma,
+                                  float* dbeta, void* stream) {
+  return tr_ln_bwd_static(d1, d2, idx2, xhat, rstd, gamma, n_rows, dz, dgamma, dbeta, (cudaStream_t)stream);
+}
+
 int gm_train_small_fwd(const float* x, int32_t K, const float* w, const float* b, int32_t O, int32_t n_rows,
                        int32_t relu, float* h, void* stream) {
   return tr_small_fwd(x, K, w, b, O, n_rows, nullptr, relu, h, (cudaStream_t)stream);

@@ -54,6 +54,9 @@ int tr_ln_fwd(const float* z, const float* g, const float* b, int M, const int* 
 size_t tr_ln_partial_floats(int M);
 int tr_ln_bwd(const float* d1, const float* d2, const int* idx2, const float* xhat, const float* rstd, const float* g,
               int M, const int* M_dev, float* dz, float* dgamma, float* dbeta, float* partial, cudaStream_t stream);
+// the same with the partials in a file-scope device array (no scratch argument, at most 65 536 rows; train_kernels.cu)
+int tr_ln_bwd_static(const float* d1, const float* d2, const int* idx2, const float* xhat, const float* rstd,
+                     const float* g, int M, float* dz, float* dgamma, float* dbeta, cudaStream_t stream);
 
 // Small first / last layers on CUDA cores.
 //   fwd:  h[r, o] = act(x[r, :K] . w[o, :K] + b[o])   (w [O][K] row-major, K, O <= 128)

@@ -10,6 +10,7 @@
 //                                        TMEM over all row tiles of a CTA; deterministic two-stage reduction
 // LayerNorm forward / backward, the 4 / 25 / 3-wide first and last layers, the loss and Adam run on CUDA cores.
 // Activations are stored fp32; every global access of the GEMM kernels is a whole 512 B row.
+#include <mutex>
 #include "train.cuh"
 
 namespace gm {
@@ -661,6 +662,48 @@ int tr_ln_bwd(const float* d1, const float* d2, const int* idx2, const float* xh
   GM_LAUNCHED(2);
   GM_LAUNCH_CHECK("tr_ln_bwd kernels");
   return GM_OK;
+}
+
+// ---- LayerNorm backward without any caller-provided or allocated scratch (gm_train_layernorm_bwd_static) ----
+// The per-block dgamma / dbeta partials live in a file-scope device array: kLnStaticMaxRows rows -> 1 024 blocks x 256
+// floats = 1 MB, held by every GPU that loads the library until the process exits.  All calls share it: calls that
+// overlap on the GPU (different streams, or two host threads) race on it.  Nothing in it has to start at zero -- every
+// block overwrites its whole 256-float slice before the reduction reads it -- so the previous call's contents are harmless.
+constexpr int kLnStaticMaxRows = 65536;
+constexpr int kLnStaticFloats = (kLnStaticMaxRows / kLnRowsPerBlock) * 2 * kTrH;
+static __device__ __align__(256) float g_ln_static_partial[kLnStaticFloats];
+
+// Device address of g_ln_static_partial on the CURRENT device, looked up once per device: in host code the array's
+// name is only a host-side stand-in for the symbol, never a pointer a kernel may dereference.
+static int ln_static_partial_ptr(float** out) {
+  constexpr int kMaxDevices = PerDeviceOnce::kMaxDevices;
+  static float* ptrs[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  GM_CUDA(cudaGetDevice(&dev));
+  GM_REQUIRE(dev >= 0 && dev < kMaxDevices, "layernorm_bwd_static: device index %d outside [0, %d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    float* p = nullptr;
+    GM_CUDA(cudaGetSymbolAddress((void**)&p, g_ln_static_partial));
+    GM_REQUIRE(p != nullptr, "layernorm_bwd_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return GM_OK;
+}
+
+int tr_ln_bwd_static(const float* d1, const float* d2, const int* idx2, const float* xhat, const float* rstd,
+                     const float* g, int M, float* dz, float* dgamma, float* dbeta, cudaStream_t stream) {
+  GM_REQUIRE(M >= 0 && M <= kLnStaticMaxRows,
+             "gm_train_layernorm_bwd_static: n_rows=%d exceeds the static scratch (at most %d rows); use "
+             "gm_train_layernorm_bwd with a caller-provided partial buffer", M, kLnStaticMaxRows);
+  GM_REQUIRE(d1 != nullptr && xhat != nullptr && rstd != nullptr && g != nullptr && dz != nullptr && dgamma != nullptr &&
+                 dbeta != nullptr, "gm_train_layernorm_bwd_static: NULL argument");
+  float* partial = nullptr;
+  int rc = ln_static_partial_ptr(&partial);
+  if (rc) return rc;
+  return tr_ln_bwd(d1, d2, idx2, xhat, rstd, g, M, nullptr, dz, dgamma, dbeta, partial, stream);
 }
 
 int tr_small_fwd(const float* x, int K, const float* w, const float* b, int O, int M, const int* M_dev, int relu,

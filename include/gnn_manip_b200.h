@@ -284,6 +284,17 @@ size_t gm_train_layernorm_partial_bytes(int32_t n_rows);
 int gm_train_layernorm_bwd(const float* d1, const float* d2, const int32_t* idx2, const float* xhat, const float* rstd,
                            const float* gamma, int32_t n_rows, float* dz, float* dgamma, float* dbeta, void* partial,
                            void* stream);
+/* gm_train_layernorm_bwd without a scratch argument.  No counterpart in the reference: added
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * The per-block dgamma / dbeta partials live in a file-scope device array of the library (1 MB on every GPU that loads it,
+ * until the process exits); the call allocates nothing.  Limit: n_rows <= GM_LN_STATIC_MAX_ROWS, larger sizes return
+ * GM_STATUS_INVALID with a message naming the limit.  Same arithmetic and order as gm_train_layernorm_bwd (dgamma / dbeta
+ * are accumulated into, dz is overwritten).  Every call shares the array: calls that overlap on the GPU (two streams, two
+ * host threads) race on it; calls ordered on one stream do not.  Nothing in it needs clearing between calls. */
+#define GM_LN_STATIC_MAX_ROWS 65536
+int gm_train_layernorm_bwd_static(const float* d1, const float* d2, const int32_t* idx2, const float* xhat,
+                                  const float* rstd, const float* gamma, int32_t n_rows, float* dz, float* dgamma,
+                                  float* dbeta, void* stream);
 int gm_train_small_fwd(const float* x, int32_t K, const float* w, const float* b, int32_t O, int32_t n_rows,
                        int32_t relu, float* h, void* stream);
 size_t gm_train_small_partial_bytes(int32_t n_rows, int32_t K, int32_t O);
