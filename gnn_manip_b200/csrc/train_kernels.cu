@@ -35,9 +35,9 @@ __device__ __forceinline__ uint32_t stg_off(int row, int col) {
 }
 
 struct GemmSmem {
-  uint64_t bar_w, bar_mma;
+  uint64_t bar_w, bar_mma[2];
   uint32_t tmem_base;
-  uint32_t pad[3];
+  uint32_t pad;
   alignas(16) float bias[kTrH];
 };
 
@@ -56,44 +56,54 @@ __device__ __forceinline__ void issue_gemm_kk(uint32_t a_s, uint32_t w_s, uint32
   }
 }
 
-__global__ void __launch_bounds__(kNT, 1) tr_gemm_kernel(TrGemmArgs a) {
+// Two tile slots per CTA (256 threads each, named barriers): the weights are shared, every slot has its own 64 KB
+// buffer -- first the bf16 hi / lo operand images, then, once the MMAs have read them, the fp32 staging tile of the
+// same rows -- and its own 128 accumulator columns.  The slots run the same serial tile loop out of phase, so that one
+// slot's global loads / stores overlap the other's conversion, MMAs and epilogue.
+constexpr int kGemmSlots = 2;
+constexpr int kGemmThreads = kGemmSlots * kNT;
+
+__global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) {
   extern __shared__ char smem_raw[];
   char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  char* A = base;                              // operand images (hi, lo)
-  char* W = base + kTrChunkBytes;              // weight images (hi, lo), resident
-  char* T = base + 2 * kTrChunkBytes;          // fp32 staging tile
-  GemmSmem* sh = reinterpret_cast<GemmSmem*>(base + 3 * kTrChunkBytes);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, q = warp & 3, hf = warp >> 2, row = q * 32 + lane;
-  const uint32_t bar_w = smem_u32(&sh->bar_w), bar_mma = smem_u32(&sh->bar_mma);
-  if (tid == 0) {
+  char* W = base;                              // weight images (hi, lo), resident
+  GemmSmem* sh = reinterpret_cast<GemmSmem*>(base + (1 + kGemmSlots) * kTrChunkBytes);
+  const int slot = threadIdx.x / kNT, tid = threadIdx.x % kNT;
+  const int lane = tid & 31, warp = tid >> 5, q = warp & 3, hf = warp >> 2, row = q * 32 + lane;
+  char* A = base + (1 + slot) * kTrChunkBytes; // operand images (hi, lo) of this slot ...
+  char* T = A;                                 // ... and, after the MMAs, its fp32 staging tile
+  const uint32_t bar_w = smem_u32(&sh->bar_w), bar_mma = smem_u32(&sh->bar_mma[slot]);
+  if (threadIdx.x == 0) {
     mbar_init(bar_w, 1);
-    mbar_init(bar_mma, 1);
+    mbar_init(smem_u32(&sh->bar_mma[0]), 1);
+    mbar_init(smem_u32(&sh->bar_mma[1]), 1);
     fence_mbar_init();
     mbar_expect_tx(bar_w, kTrChunkBytes);
     for (int i = 0; i < 4; ++i) bulk_g2s(smem_u32(W) + i * kKBlock, (const char*)a.chunk + (size_t)i * kKBlock, kKBlock, bar_w);
   }
-  if (warp == 0) {
-    tmem_alloc(smem_u32(&sh->tmem_base), 128);
+  if (threadIdx.x < 32) {
+    tmem_alloc(smem_u32(&sh->tmem_base), 128 * kGemmSlots);
     tmem_relinquish();
   }
-  for (int i = tid; i < kTrH; i += kNT) sh->bias[i] = a.bias ? a.bias[i] : 0.f;
+  for (int i = threadIdx.x; i < kTrH; i += kGemmThreads) sh->bias[i] = a.bias ? a.bias[i] : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = sh->tmem_base;
+  const uint32_t tmem = sh->tmem_base + 128u * slot;
   const int M = a.M_dev ? min(*a.M_dev, a.M) : a.M;
   const int n_tiles = (M + kT - 1) / kT;
   constexpr int R = kT / (kNT / 32);           // 16 rows per warp in the row-wise phases
   uint32_t ph = 0;
   bool w_ready = false;
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  for (int tile = blockIdx.x + slot * gridDim.x; tile < n_tiles; tile += kGemmSlots * gridDim.x) {
     const int row0 = tile * kT, rows_valid = min(kT, M - row0);
     // ---- X rows -> bf16 hi / lo operand images (warp per row, coalesced 512 B) ----
-    {
-      float4 x[R];
 #pragma unroll
-      for (int i = 0; i < R; ++i) {
-        const int r = warp * R + i;
+    for (int i0 = 0; i0 < R; i0 += 8) {
+      float4 x[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = warp * R + i0 + i;
         x[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (r < rows_valid) {
           const size_t src = a.in_idx ? (size_t)a.in_idx[row0 + r] : (size_t)(row0 + r);
@@ -101,8 +111,8 @@ __global__ void __launch_bounds__(kNT, 1) tr_gemm_kernel(TrGemmArgs a) {
         }
       }
 #pragma unroll
-      for (int i = 0; i < R; ++i) {
-        const int r = warp * R + i;
+      for (int i = 0; i < 8; ++i) {
+        const int r = warp * R + i0 + i;
         uint2 hi, lo;
         split_bf16x2(x[i].x, x[i].y, hi.x, lo.x);
         split_bf16x2(x[i].z, x[i].w, hi.y, lo.y);
@@ -113,7 +123,7 @@ __global__ void __launch_bounds__(kNT, 1) tr_gemm_kernel(TrGemmArgs a) {
     }
     fence_proxy_async_smem();
     tc_fence_before();
-    __syncthreads();
+    named_bar_sync(1 + slot, kNT);
     if (tid == 0) {
       if (!w_ready) mbar_wait(bar_w, 0);
       tc_fence_after();
@@ -122,7 +132,7 @@ __global__ void __launch_bounds__(kNT, 1) tr_gemm_kernel(TrGemmArgs a) {
     }
     w_ready = true;
     __syncwarp();
-    mbar_wait(bar_mma, ph);
+    mbar_wait(bar_mma, ph);                    // the MMAs have read the operand images: the buffer becomes the staging tile
     ph ^= 1u;
     tc_fence_after();
     // ---- accumulator (+ bias) -> staging tile: thread = (row, column half) ----
@@ -140,7 +150,7 @@ __global__ void __launch_bounds__(kNT, 1) tr_gemm_kernel(TrGemmArgs a) {
       }
     }
     tc_fence_before();
-    __syncthreads();
+    named_bar_sync(1 + slot, kNT);
     // ---- row-wise epilogue: every global access is one coalesced 512 B row ----
 #pragma unroll 4
     for (int i = 0; i < R; ++i) {
@@ -168,14 +178,14 @@ __global__ void __launch_bounds__(kNT, 1) tr_gemm_kernel(TrGemmArgs a) {
       }
       *dst = v;
     }
-    __syncthreads();                           // T and A are rewritten by the next tile
+    named_bar_sync(1 + slot, kNT);             // the buffer is rewritten by the slot's next tile
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 128);
+  if (threadIdx.x < 32) tmem_dealloc(sh->tmem_base, 128 * kGemmSlots);
 }
 
-constexpr int kGemmSmem = 3 * kTrChunkBytes + (int)sizeof(GemmSmem) + 1024;
+constexpr int kGemmSmem = (1 + kGemmSlots) * kTrChunkBytes + (int)sizeof(GemmSmem) + 1024;
 
 // ---- weight packing (batched): fp32 [128][ld] block -> bf16 hi / lo swizzled K-major images ----
 __global__ void tr_pack_kernel(const TrPackJob* __restrict__ jobs) {
@@ -367,7 +377,7 @@ int tr_gemm(const TrGemmArgs& a, cudaStream_t stream) {
     once.finish(dev);
   }
   const int grid = min(ceil_div(a.M, kT), kNumSMs);
-  tr_gemm_kernel<<<grid, kNT, kGemmSmem, stream>>>(a);
+  tr_gemm_kernel<<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("tr_gemm_kernel");
   return GM_OK;
@@ -489,7 +499,22 @@ tr_ln_bwd_kernel(const float* __restrict__ d1, const float* __restrict__ d2, con
   }
 }
 
-// out[i] += sum_b partial[b][i] in a fixed order (i < width); n_blocks may come from a device row count
+// out[i] += sum_b partial[b][i] in a fixed order (i < width), in two levels: groups of kRedChunk consecutive blocks are
+// summed in place into the group's first row (one block of threads per group), then the group rows are summed by one
+// thread per column.  n_blocks may come from a device row count.
+constexpr int kRedChunk = 64;
+__global__ void tr_partial_group_kernel(float* __restrict__ partial, int n_blocks_max, int rows_per_block,
+                                        const int* __restrict__ M_dev, int width) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= width) return;
+  int nb = n_blocks_max;
+  if (M_dev) nb = min(nb, (*M_dev + rows_per_block - 1) / rows_per_block);
+  const int b0 = blockIdx.y * kRedChunk, b1 = min(b0 + kRedChunk, nb);
+  if (b0 + 1 >= b1) return;
+  float t = 0.f;
+  for (int b = b0; b < b1; ++b) t += partial[(size_t)b * width + i];
+  partial[(size_t)b0 * width + i] = t;
+}
 __global__ void tr_partial_reduce_kernel(const float* __restrict__ partial, int n_blocks_max, int rows_per_block,
                                          const int* __restrict__ M_dev, int width, float* __restrict__ out0,
                                          float* __restrict__ out1, int split) {
@@ -498,9 +523,15 @@ __global__ void tr_partial_reduce_kernel(const float* __restrict__ partial, int 
   int nb = n_blocks_max;
   if (M_dev) nb = min(nb, (*M_dev + rows_per_block - 1) / rows_per_block);
   float t = 0.f;
-  for (int b = 0; b < nb; ++b) t += partial[(size_t)b * width + i];
+  for (int b = 0; b < nb; b += kRedChunk) t += partial[(size_t)b * width + i];
   if (i < split) out0[i] += t;
   else if (out1) out1[i - split] += t;
+}
+static void launch_partial_reduce(float* partial, int nb, int rows_per_block, const int* M_dev, int width, float* out0,
+                                  float* out1, int split, cudaStream_t stream) {
+  const int bx = ceil_div(width, 256);
+  tr_partial_group_kernel<<<dim3(bx, ceil_div(nb, kRedChunk)), 256, 0, stream>>>(partial, nb, rows_per_block, M_dev, width);
+  tr_partial_reduce_kernel<<<bx, 256, 0, stream>>>(partial, nb, rows_per_block, M_dev, width, out0, out1, split);
 }
 
 // ---- small layers: x [M, K], w [O][K]; a block handles kSmallRows rows ----
@@ -658,8 +689,8 @@ int tr_ln_bwd(const float* d1, const float* d2, const int* idx2, const float* xh
   if (M <= 0) return GM_OK;
   const int nb = ceil_div(M, kLnRowsPerBlock);
   tr_ln_bwd_kernel<<<nb, kLnWarps * 32, 0, stream>>>(d1, d2, idx2, xhat, rstd, g, M, M_dev, dz, partial);
-  tr_partial_reduce_kernel<<<1, 2 * kTrH, 0, stream>>>(partial, nb, kLnRowsPerBlock, M_dev, 2 * kTrH, dgamma, dbeta, kTrH);
-  GM_LAUNCHED(2);
+  launch_partial_reduce(partial, nb, kLnRowsPerBlock, M_dev, 2 * kTrH, dgamma, dbeta, kTrH, stream);
+  GM_LAUNCHED(3);
   GM_LAUNCH_CHECK("tr_ln_bwd kernels");
   return GM_OK;
 }
@@ -734,8 +765,8 @@ int tr_small_bwd(const float* x, int K, const float* w, int O, const float* dh, 
   }
   const int nb = ceil_div(M, kSmallRows), width = O * K + O;
   tr_small_bwd_kernel<<<nb, 256, smem, stream>>>(x, K, w, O, dh, mask, M, M_dev, dx, dx_mask, partial);
-  tr_partial_reduce_kernel<<<ceil_div(width, 256), 256, 0, stream>>>(partial, nb, kSmallRows, M_dev, width, dW, db, O * K);
-  GM_LAUNCHED(2);
+  launch_partial_reduce(partial, nb, kSmallRows, M_dev, width, dW, db, O * K, stream);
+  GM_LAUNCHED(3);
   GM_LAUNCH_CHECK("tr_small_bwd kernels");
   return GM_OK;
 }
