@@ -56,6 +56,8 @@ __device__ __forceinline__ void issue_gemm_kk(uint32_t a_s, uint32_t w_s, uint32
   }
 }
 
+__device__ __forceinline__ void prefetch_l2_line(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // Two tile slots per CTA (256 threads each, named barriers): the weights are shared, every slot has its own 64 KB
 // buffer -- first the bf16 hi / lo operand images, then, once the MMAs have read them, the fp32 staging tile of the
 // same rows -- and its own 128 accumulator columns.  The slots run the same serial tile loop out of phase, so that one
@@ -121,6 +123,22 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
         *reinterpret_cast<uint2*>(A + kImage + o) = lo;
       }
     }
+    // The tile loop is a chain of dependent phases, so its global reads are requested well ahead: the X rows of this
+    // slot's NEXT tile and the mask / accumulate rows of this tile's epilogue are pulled into L2 now (lane l: 128-byte
+    // line l & 3 of row l >> 2, sixteen rows per warp in two steps).
+    {
+      const int nt = tile + kGemmSlots * (int)gridDim.x;
+#pragma unroll
+      for (int k2 = 0; k2 < 2; ++k2) {
+        const int r = warp * R + 8 * k2 + (lane >> 2);
+        const size_t off = (size_t)r * kTrH + 32 * (lane & 3);
+        if (nt < n_tiles && a.in_idx == nullptr && nt * kT + r < M) prefetch_l2_line(a.x + (size_t)nt * kT * kTrH + off);
+        if (r < rows_valid) {
+          if (a.mask) prefetch_l2_line(a.mask + (size_t)row0 * kTrH + off);
+          if (a.accumulate) prefetch_l2_line(a.out + (size_t)row0 * kTrH + off);
+        }
+      }
+    }
     fence_proxy_async_smem();
     tc_fence_before();
     named_bar_sync(1 + slot, kNT);
@@ -132,6 +150,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
     }
     w_ready = true;
     __syncwarp();
+    // source rows of the gathered adds for this warp's 16 rows (lane i < 16: row i), fetched under the MMAs
+    int my_i1, my_i2;
+    {
+      const int rr = warp * R + (lane & 15);
+      const bool rv = rr < rows_valid;
+      my_i1 = (a.idx1 && rv) ? __ldg(a.idx1 + row0 + rr) : row0 + rr;
+      my_i2 = (a.idx2 && rv) ? __ldg(a.idx2 + row0 + rr) : row0 + rr;
+      if (!rv) my_i1 = my_i2 = 0;
+    }
     mbar_wait(bar_mma, ph);                    // the MMAs have read the operand images: the buffer becomes the staging tile
     ph ^= 1u;
     tc_fence_after();
@@ -151,32 +178,39 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
     }
     tc_fence_before();
     named_bar_sync(1 + slot, kNT);
-    // ---- row-wise epilogue: every global access is one coalesced 512 B row ----
-#pragma unroll 4
-    for (int i = 0; i < R; ++i) {
-      const int r = warp * R + i;
-      if (r >= rows_valid) break;
-      const size_t gr = (size_t)(row0 + r);
-      float4 v = *reinterpret_cast<const float4*>(T + stg_off(r, 4 * lane));
-      if (a.add1) {
-        const float4 t = __ldg(reinterpret_cast<const float4*>(a.add1 + (a.idx1 ? (size_t)a.idx1[gr] : gr) * kTrH) + lane);
-        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+    // ---- row-wise epilogue: every global access is one coalesced 512 B row; four rows per step with all their
+    //      loads (gathered adds, mask, accumulate target) issued before the first use ----
+#pragma unroll 1
+    for (int i0 = 0; i0 < R; i0 += 4) {
+      float4 t1[4], t2[4], mk[4], oo[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = warp * R + i0 + i;
+        const bool ok = r < rows_valid;
+        const size_t gr = (size_t)(row0 + r);
+        const int s1 = __shfl_sync(0xffffffffu, my_i1, i0 + i), s2 = __shfl_sync(0xffffffffu, my_i2, i0 + i);
+        t1[i] = t2[i] = mk[i] = oo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.add1 && ok) t1[i] = __ldg(reinterpret_cast<const float4*>(a.add1 + (size_t)s1 * kTrH) + lane);
+        if (a.add2 && ok) t2[i] = __ldg(reinterpret_cast<const float4*>(a.add2 + (size_t)s2 * kTrH) + lane);
+        if (a.mask && ok) mk[i] = __ldg(reinterpret_cast<const float4*>(a.mask + gr * kTrH) + lane);
+        if (a.accumulate && ok) oo[i] = *(reinterpret_cast<const float4*>(a.out + gr * kTrH) + lane);
       }
-      if (a.add2) {
-        const float4 t = __ldg(reinterpret_cast<const float4*>(a.add2 + (a.idx2 ? (size_t)a.idx2[gr] : gr) * kTrH) + lane);
-        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = warp * R + i0 + i;
+        if (r < rows_valid) {
+          float4 v = *reinterpret_cast<const float4*>(T + stg_off(r, 4 * lane));
+          if (a.add1) { v.x += t1[i].x; v.y += t1[i].y; v.z += t1[i].z; v.w += t1[i].w; }
+          if (a.add2) { v.x += t2[i].x; v.y += t2[i].y; v.z += t2[i].z; v.w += t2[i].w; }
+          if (a.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+          if (a.mask) {
+            v.x = mk[i].x > 0.f ? v.x : 0.f; v.y = mk[i].y > 0.f ? v.y : 0.f;
+            v.z = mk[i].z > 0.f ? v.z : 0.f; v.w = mk[i].w > 0.f ? v.w : 0.f;
+          }
+          if (a.accumulate) { v.x += oo[i].x; v.y += oo[i].y; v.z += oo[i].z; v.w += oo[i].w; }
+          *(reinterpret_cast<float4*>(a.out + (size_t)(row0 + r) * kTrH) + lane) = v;
+        }
       }
-      if (a.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-      if (a.mask) {
-        const float4 m = __ldg(reinterpret_cast<const float4*>(a.mask + gr * kTrH) + lane);
-        v.x = m.x > 0.f ? v.x : 0.f; v.y = m.y > 0.f ? v.y : 0.f; v.z = m.z > 0.f ? v.z : 0.f; v.w = m.w > 0.f ? v.w : 0.f;
-      }
-      float4* dst = reinterpret_cast<float4*>(a.out + gr * kTrH) + lane;
-      if (a.accumulate) {
-        const float4 o = *dst;
-        v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
-      }
-      *dst = v;
     }
     named_bar_sync(1 + slot, kNT);             // the buffer is rewritten by the slot's next tile
   }

@@ -1,7 +1,7 @@
 #!/bin/bash
-# launch list of the training step (C5): plain run first, then ncu per-launch durations
+# launch list of ONE training step (C5): plain run first, then ncu per-launch durations
 mkdir -p gpurun_out
-CMD="python bench.py --workload c5 --steps 1 --warmup 3 --no-cpu-baseline"
-timeout 300 $CMD > gpurun_out/plain_c5.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none -c 6000 --csv --log-file gpurun_out/launches_c5.csv $CMD > gpurun_out/ncu_c5.log 2>&1
+CMD="python tools_train_launches.py"
+timeout 300 $CMD > gpurun_out/plain_c5.log 2>&1 && timeout 600 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --cache-control none --csv --log-file gpurun_out/launches_c5.csv $CMD > gpurun_out/ncu_c5.log 2>&1
 echo "rc=$?"; tail -2 gpurun_out/ncu_c5.log | cut -c1-300
-python profiles/summarise_launches.py gpurun_out/launches_c5.csv | head -40
+python profiles/summarise_launches.py gpurun_out/launches_c5.csv | head -16
