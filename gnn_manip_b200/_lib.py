@@ -90,6 +90,10 @@ SIGNATURES = {
     "gm_forward_workspace_bytes": (c_size_t, [c_void_p, c_int32, c_int32, c_int32]),
     "gm_model_forward": (ctypes.c_int, [c_void_p, c_int32, c_void_p, c_void_p, c_void_p, c_int32, c_double, c_int32,
                                         c_int32] + [c_void_p] * 7 + [c_size_t, c_void_p]),
+    "gm_encode": (ctypes.c_int, [c_void_p, c_int32, c_void_p, c_void_p, c_void_p, c_int32, c_double, c_int32, c_int32] +
+                  [c_void_p] * 6 + [c_size_t, c_void_p]),
+    "gm_mp_step": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, c_int32] + [c_void_p] * 5 + [c_size_t, c_void_p]),
+    "gm_decode": (ctypes.c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p, c_size_t, c_void_p]),
     "gm_model_forward_profile": (ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_double, c_int32,
                                                 c_int32] + [c_void_p] * 7 + [c_size_t, c_void_p, POINTER(c_float),
                                                                              POINTER(c_int32)]),

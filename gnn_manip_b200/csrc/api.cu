@@ -233,10 +233,9 @@ void carve_forward(Arena& a, const gm_model* m, int n_nodes, int max_edges, bool
 
 bool use_tc(const gm_model* m, int impl) { return impl == GM_IMPL_TC || (impl == GM_IMPL_AUTO && m->tc_ok); }
 
-int forward_simt(const gm_model* m, const float* nodes, const float* edge_attr, const float* pos, int pos_stride,
-                 float conn_r, int n_nodes, int max_edges, const int* n_edges_dev, const int* recv_ptr,
-                 const int* esend, const int* erecv, const int* eref, float* pred, const FwdWs& w,
-                 cudaStream_t st) {
+int simt_encode(const gm_model* m, const float* nodes, const float* edge_attr, const float* pos, int pos_stride,
+                float conn_r, int n_nodes, int max_edges, const int* n_edges_dev, const int* esend, const int* erecv,
+                const int* eref, const FwdWs& w, cudaStream_t st) {
   int rc;
   // encoder: edges (receiver-major order) and nodes
   MlpSimtArgs a = simt_args(m->enc_edge);
@@ -255,31 +254,58 @@ int forward_simt(const gm_model* m, const float* nodes, const float* edge_attr, 
   a = simt_args(m->enc_node);
   a.n_src = 1; a.src[0] = nodes; a.width[0] = m->node_dim; a.src_stride[0] = m->node_dim;
   a.M = n_nodes; a.out = w.v;
-  if ((rc = mlp_simt(a, st))) return rc;
+  return mlp_simt(a, st);
+}
+
+int simt_mp_step(const gm_model* m, int s, int n_nodes, int max_edges, const int* n_edges_dev, const int* recv_ptr,
+                 const int* esend, const int* erecv, const FwdWs& w, cudaStream_t st) {
+  int rc;
   const int H = m->hidden;
-  for (int s = 0; s < m->m_steps; ++s) {
-    a = simt_args(m->proc_edge[s]);          // phi_edge(cat[e, v[recv], v[send]])  (graph_networks.py:43-50)
-    a.n_src = 3;
-    a.src[0] = w.e; a.idx[0] = nullptr;
-    a.src[1] = w.v; a.idx[1] = erecv;
-    a.src[2] = w.v; a.idx[2] = esend;
-    for (int i = 0; i < 3; ++i) { a.width[i] = H; a.src_stride[i] = H; }
-    a.M = max_edges; a.M_dev = n_edges_dev;
-    a.out_pre = w.eo; a.out = w.e; a.residual = w.e;
-    if ((rc = mlp_simt(a, st))) return rc;
-    if ((rc = segment_sum(w.eo, H, recv_ptr, nullptr, n_nodes, w.aggpart, st))) return rc;
-    a = simt_args(m->proc_node[s]);          // phi_node(cat[agg, v])  (graph_networks.py:75-85)
-    a.n_src = 2;
-    a.src[0] = w.aggpart; a.src[1] = w.v;
-    for (int i = 0; i < 2; ++i) { a.width[i] = H; a.src_stride[i] = H; a.idx[i] = nullptr; }
-    a.M = n_nodes; a.out = w.v; a.residual = w.v;
-    if ((rc = mlp_simt(a, st))) return rc;
-  }
-  a = simt_args(m->dec);
+  MlpSimtArgs a = simt_args(m->proc_edge[s]);          // phi_edge(cat[e, v[recv], v[send]])  (graph_networks.py:43-50)
+  a.n_src = 3;
+  a.src[0] = w.e; a.idx[0] = nullptr;
+  a.src[1] = w.v; a.idx[1] = erecv;
+  a.src[2] = w.v; a.idx[2] = esend;
+  for (int i = 0; i < 3; ++i) { a.width[i] = H; a.src_stride[i] = H; }
+  a.M = max_edges; a.M_dev = n_edges_dev;
+  a.out_pre = w.eo; a.out = w.e; a.residual = w.e;
+  if ((rc = mlp_simt(a, st))) return rc;
+  if ((rc = segment_sum(w.eo, H, recv_ptr, nullptr, n_nodes, w.aggpart, st))) return rc;
+  a = simt_args(m->proc_node[s]);          // phi_node(cat[agg, v])  (graph_networks.py:75-85)
+  a.n_src = 2;
+  a.src[0] = w.aggpart; a.src[1] = w.v;
+  for (int i = 0; i < 2; ++i) { a.width[i] = H; a.src_stride[i] = H; a.idx[i] = nullptr; }
+  a.M = n_nodes; a.out = w.v; a.residual = w.v;
+  return mlp_simt(a, st);
+}
+
+int simt_decode(const gm_model* m, int n_nodes, float* pred, const FwdWs& w, cudaStream_t st) {
+  const int H = m->hidden;
+  MlpSimtArgs a = simt_args(m->dec);
   a.n_src = 1; a.src[0] = w.v; a.width[0] = H; a.src_stride[0] = H;
   a.M = n_nodes; a.out = pred;
-  if ((rc = mlp_simt(a, st))) return rc;
-  return GM_OK;
+  return mlp_simt(a, st);
+}
+
+int forward_simt(const gm_model* m, const float* nodes, const float* edge_attr, const float* pos, int pos_stride,
+                 float conn_r, int n_nodes, int max_edges, const int* n_edges_dev, const int* recv_ptr,
+                 const int* esend, const int* erecv, const int* eref, float* pred, const FwdWs& w,
+                 cudaStream_t st) {
+  int rc;
+  if ((rc = simt_encode(m, nodes, edge_attr, pos, pos_stride, conn_r, n_nodes, max_edges, n_edges_dev, esend, erecv, eref,
+                        w, st)))
+    return rc;
+  for (int s = 0; s < m->m_steps; ++s)
+    if ((rc = simt_mp_step(m, s, n_nodes, max_edges, n_edges_dev, recv_ptr, esend, erecv, w, st))) return rc;
+  return simt_decode(m, n_nodes, pred, w, st);
+}
+
+// node half of MP step s: the 16-warp kernel (mp_node16.cu); GM_NODE_KERNEL=8 selects the 8-warp kernel of mp_tc.cu (A/B aid)
+int tc_node_half(const gm_model* m, int s, const TcMlp* next_edge, const TcMlp* dec, float* pred, const TcGraph& g,
+                 const TcBuffers& b, cudaStream_t st) {
+  static const bool node8 = [] { const char* e = getenv("GM_NODE_KERNEL"); return e && !strcmp(e, "8"); }();
+  return node8 ? tc_mp_node(m->tc_proc_node[s], next_edge, dec, m->out_dim, pred, g, b, st)
+               : tc_mp_node16(m->tc_proc_node[s], next_edge, dec, m->out_dim, pred, g, b, st);
 }
 
 int forward_tc(const gm_model* m, const float* nodes, const float* edge_attr, const float* pos, int pos_stride,
@@ -307,12 +333,7 @@ int forward_tc(const gm_model* m, const float* nodes, const float* edge_attr, co
     if ((rc = tc_mp_edge(m->tc_proc_edge[s], g, b, st, !(s == 0 && enc_node_done != nullptr)))) return rc;
     GM_PROF(kProfMpNode);
     const bool last = s + 1 == m->m_steps;
-    // node half: the 16-warp kernel (mp_node16.cu); GM_NODE_KERNEL=8 selects the 8-warp kernel of mp_tc.cu (A/B aid)
-    static const bool node8 = [] { const char* e = getenv("GM_NODE_KERNEL"); return e && !strcmp(e, "8"); }();
-    rc = node8 ? tc_mp_node(m->tc_proc_node[s], last ? nullptr : &m->tc_proc_edge[s + 1], last ? &m->tc_dec : nullptr,
-                            m->out_dim, pred, g, b, st)
-               : tc_mp_node16(m->tc_proc_node[s], last ? nullptr : &m->tc_proc_edge[s + 1], last ? &m->tc_dec : nullptr,
-                              m->out_dim, pred, g, b, st);
+    rc = tc_node_half(m, s, last ? nullptr : &m->tc_proc_edge[s + 1], last ? &m->tc_dec : nullptr, pred, g, b, st);
     if (rc) return rc;
   }
   GM_PROF(-1);
@@ -651,6 +672,80 @@ int gm_model_forward(const gm_model* model, int32_t impl, const float* nodes, co
                       recv_ptr, esend, erecv, eref, pred, w, (cudaStream_t)stream);
   return forward_simt(model, nodes, edge_attr, pos, pos_stride, (float)conn_r, n_nodes, max_edges, n_edges_dev,
                       recv_ptr, esend, erecv, eref, pred, w, (cudaStream_t)stream);
+}
+
+// ---- the three stages of EncProcDecGNN.forward as separate calls (epd_gnn.py:88-96); the latents live in the workspace
+//      between the calls (same layout as gm_model_forward: gm_forward_workspace_bytes) ----
+namespace {
+int staged_ws(const char* who, const gm_model* model, int32_t impl, int32_t n_nodes, int32_t max_edges, void* workspace,
+              size_t workspace_bytes, bool* tc, gm::FwdWs* w) {
+  GM_REQUIRE(model != nullptr, "%s: model is NULL", who);
+  GM_REQUIRE(n_nodes > 0 && max_edges >= 0, "%s: bad sizes", who);
+  *tc = gm::use_tc(model, impl);
+  GM_REQUIRE(!*tc || model->tc_ok, "%s: model shape (hidden=%d, num_layers=%d) is not covered by the tcgen05 kernels", who,
+             model->hidden, model->num_layers);
+  gm::Arena a(workspace, workspace_bytes);
+  gm::carve_forward(a, model, n_nodes, max_edges, !*tc, *w);
+  if (!a.ok || workspace == nullptr) {
+    gm::set_error("%s: workspace too small (%zu < %zu bytes)", who, workspace_bytes, a.off);
+    return gm::GM_ERR_WORKSPACE;
+  }
+  return gm::GM_OK;
+}
+}  // namespace
+
+int gm_encode(const gm_model* model, int32_t impl, const float* nodes, const float* edge_attr, const float* pos,
+              int32_t pos_stride, double conn_r, int32_t n_nodes, int32_t max_edges, const int32_t* n_edges_dev,
+              const int32_t* recv_ptr, const int32_t* esend, const int32_t* erecv, const int32_t* eref, void* workspace,
+              size_t workspace_bytes, void* stream) {
+  GM_REQUIRE(nodes != nullptr && n_edges_dev != nullptr, "gm_encode: NULL argument");
+  GM_REQUIRE(edge_attr != nullptr || pos != nullptr, "gm_encode: need edge_attr or pos");
+  bool tc;
+  FwdWs w;
+  int rc = staged_ws("gm_encode", model, impl, n_nodes, max_edges, workspace, workspace_bytes, &tc, &w);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!tc)
+    return simt_encode(model, nodes, edge_attr, pos, pos_stride, (float)conn_r, n_nodes, max_edges, n_edges_dev, esend,
+                       erecv, eref, w, st);
+  TcGraph g{n_edges_dev, max_edges, n_nodes, esend, erecv, recv_ptr};
+  TcBuffers b{w.e, w.v, w.pr, w.ps, w.aggpart, w.carry};
+  if ((rc = tc_enc_edge(model->tc_enc_edge, model->edge_dim, pos, pos_stride, (float)conn_r, edge_attr, eref, g, b, st)))
+    return rc;
+  return tc_enc_node(model->tc_enc_node, model->tc_proc_edge[0], model->node_dim, nodes, g, b, st);
+}
+
+int gm_mp_step(const gm_model* model, int32_t impl, int32_t step, int32_t n_nodes, int32_t max_edges,
+               const int32_t* n_edges_dev, const int32_t* recv_ptr, const int32_t* esend, const int32_t* erecv,
+               void* workspace, size_t workspace_bytes, void* stream) {
+  GM_REQUIRE(n_edges_dev != nullptr && recv_ptr != nullptr && esend != nullptr && erecv != nullptr,
+             "gm_mp_step: NULL argument");
+  bool tc;
+  FwdWs w;
+  int rc = staged_ws("gm_mp_step", model, impl, n_nodes, max_edges, workspace, workspace_bytes, &tc, &w);
+  if (rc) return rc;
+  GM_REQUIRE(step >= 0 && step < model->m_steps, "gm_mp_step: step=%d outside [0, %d)", step, model->m_steps);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!tc) return simt_mp_step(model, step, n_nodes, max_edges, n_edges_dev, recv_ptr, esend, erecv, w, st);
+  TcGraph g{n_edges_dev, max_edges, n_nodes, esend, erecv, recv_ptr};
+  TcBuffers b{w.e, w.v, w.pr, w.ps, w.aggpart, w.carry};
+  // (an ordinary, fully ordered launch: the caller may have touched the latents between the stages)
+  if ((rc = tc_mp_edge(model->tc_proc_edge[step], g, b, st, false))) return rc;
+  // the node half also prepares Pr / Ps for the following edge step; after the last step there is none and the
+  // (unused) projections are taken with this step's own edge MLP, the decoder being a stage of its own here
+  const int nx = step + 1 < model->m_steps ? step + 1 : step;
+  return tc_node_half(model, step, &model->tc_proc_edge[nx], nullptr, nullptr, g, b, st);
+}
+
+int gm_decode(const gm_model* model, int32_t impl, int32_t n_nodes, int32_t max_edges, float* pred, void* workspace,
+              size_t workspace_bytes, void* stream) {
+  GM_REQUIRE(pred != nullptr, "gm_decode: pred is NULL");
+  bool tc;
+  FwdWs w;
+  int rc = staged_ws("gm_decode", model, impl, n_nodes, max_edges, workspace, workspace_bytes, &tc, &w);
+  if (rc) return rc;
+  // on both paths the decoder MLP runs on CUDA cores in fp32 (gm_model_forward fuses it into the last node kernel)
+  return simt_decode(model, n_nodes, pred, w, (cudaStream_t)stream);
 }
 
 int gm_model_forward_profile(const gm_model* model, const float* nodes, const float* edge_attr, const float* pos,

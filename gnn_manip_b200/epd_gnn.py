@@ -65,6 +65,7 @@ class EncProcDecGNN(nn.Module):
                                                      phi_node=self._build_mlp(2 * h, h, h, num_layers, True)))
         self.decoder = self._build_mlp(h, h, out_dim, num_layers, False)
         self.impl = int(os.environ.get("GNN_MANIP_B200_IMPL", _lib.GM_IMPL_AUTO))
+        self.staged = False      # True: forward() calls gm_encode / gm_mp_step / gm_decode instead of gm_model_forward
         self._packed = {}      # device -> (version key, PackedModel)
         self._fwd_cache = {}   # device -> {"ws": (key, tensor), "csr": (key, (recv_ptr, esend, erecv, eref, n_edges))}
 
@@ -152,7 +153,17 @@ class EncProcDecGNN(nn.Module):
             ws = hit[1]
             if E == 0:
                 ea = torch.zeros((1, self.edge_dim), dtype=torch.float32, device=dev)
-            check(L.gm_model_forward(pm.handle, self.impl, ptr(x), ptr(ea), None, 0, 0.0, N, E, ptr(n_edges),
-                                     ptr(recv_ptr), ptr(esend), ptr(erecv), ptr(eref), ptr(pred), ptr(ws), ws_bytes,
-                                     stream_ptr(dev)), "gm_model_forward")
+            if not self.staged:
+                check(L.gm_model_forward(pm.handle, self.impl, ptr(x), ptr(ea), None, 0, 0.0, N, E, ptr(n_edges),
+                                         ptr(recv_ptr), ptr(esend), ptr(erecv), ptr(eref), ptr(pred), ptr(ws), ws_bytes,
+                                         stream_ptr(dev)), "gm_model_forward")
+            else:
+                # the reference's own structure (epd_gnn.py:88-96): encoder, one call per processor block, decoder
+                st = stream_ptr(dev)
+                check(L.gm_encode(pm.handle, self.impl, ptr(x), ptr(ea), None, 0, 0.0, N, E, ptr(n_edges), ptr(recv_ptr),
+                                  ptr(esend), ptr(erecv), ptr(eref), ptr(ws), ws_bytes, st), "gm_encode")
+                for step in range(self.m_steps):
+                    check(L.gm_mp_step(pm.handle, self.impl, step, N, E, ptr(n_edges), ptr(recv_ptr), ptr(esend),
+                                       ptr(erecv), ptr(ws), ws_bytes, st), "gm_mp_step")
+                check(L.gm_decode(pm.handle, self.impl, N, E, ptr(pred), ptr(ws), ws_bytes, st), "gm_decode")
         return pred.to(out_dev)

@@ -136,6 +136,24 @@ int gm_model_forward(const gm_model* model, int32_t impl, const float* nodes, co
                      const int32_t* erecv, const int32_t* eref, float* pred, void* workspace,
                      size_t workspace_bytes, void* stream);
 
+/* The three stages of EncProcDecGNN.forward as separate calls, for a caller that keeps the reference's structure
+ * (encoder -> for in_module in processor: _process -> decoder; gnn_manip/models/epd_gnn.py:86-105).  The latents (and, on
+ * the tensor path, the projections Pr / Ps of the next edge step) live in `workspace` between the calls: same size and
+ * layout as gm_model_forward (gm_forward_workspace_bytes with the same impl), same graph arrays in every call.
+ *   gm_encode   epd_gnn.py:88     latent_node_0, latent_edge_0 (edge features from edge_attr or, if NULL, from pos)
+ *   gm_mp_step  epd_gnn.py:99-105 one processor block incl. both residuals; step = 0 .. m_steps - 1, in order
+ *   gm_decode   epd_gnn.py:96     pred [n_nodes, out_dim]; fp32 CUDA-core MLP on both paths (gm_model_forward fuses the
+ *                                 decoder into the last node kernel instead) */
+int gm_encode(const gm_model* model, int32_t impl, const float* nodes, const float* edge_attr, const float* pos,
+              int32_t pos_stride, double conn_r, int32_t n_nodes, int32_t max_edges, const int32_t* n_edges_dev,
+              const int32_t* recv_ptr, const int32_t* esend, const int32_t* erecv, const int32_t* eref, void* workspace,
+              size_t workspace_bytes, void* stream);
+int gm_mp_step(const gm_model* model, int32_t impl, int32_t step, int32_t n_nodes, int32_t max_edges,
+               const int32_t* n_edges_dev, const int32_t* recv_ptr, const int32_t* esend, const int32_t* erecv,
+               void* workspace, size_t workspace_bytes, void* stream);
+int gm_decode(const gm_model* model, int32_t impl, int32_t n_nodes, int32_t max_edges, float* pred, void* workspace,
+              size_t workspace_bytes, void* stream);
+
 /* Same forward on the tcgen05 path with a CUDA event recorded on `stream` before every kernel; synchronises the
  * stream and returns per-kernel-class device time: ms_host[4] / launches_host[4] for
  * {edge encoder, node encoder, mp_edge (edge MLP + segmented sum), mp_node (node MLP + projections / decoder)}.

@@ -259,6 +259,39 @@ def test_forward_matches_reference_golden(gm, oracle_lib, impl, tol):
 
 
 @pytest.mark.parametrize("impl,tol", [(1, ACC_TOL_SIMT), (2, ACC_TOL_TC)])
+def test_staged_forward_encode_mp_step_decode(gm, oracle_lib, impl, tol):
+    """gm_encode / gm_mp_step / gm_decode (the reference's own structure, epd_gnn.py:88-96) against the reference golden
+    and against the one-call forward: the fp32 path is the same kernels (bit-identical); on the tensor path only the
+    decoder differs (fp32 CUDA cores instead of the fused tcgen05 decoder)."""
+    g = load_golden("step")
+    _, mine = seeded_models(gm, oracle_lib, int(g["weights_seed"]))
+    mine.impl = impl
+    nodes, edge_attr = torch.from_numpy(g["nodes"]), torch.from_numpy(g["edge_attr"])
+    ei = torch.from_numpy(g["edge_index"].astype(np.int64))
+    whole = mine(nodes, edge_attr, ei)
+    mine.staged = True
+    staged = mine(nodes, edge_attr, ei)
+    mine.staged = False
+    assert rel_l2(staged, g["pred"]) < tol
+    if impl == 1:
+        assert torch.equal(staged, whole)
+    else:
+        assert rel_l2(staged, whole) < 1e-4     # decoder arithmetic only (measured 1.4e-5)
+    L, lib = gm._lib.lib(), gm._lib
+    pm = mine.packed(torch.device("cuda", 0))
+    ws = torch.empty((1024,), dtype=torch.uint8, device="cuda")
+    idx = torch.zeros((8,), dtype=torch.int32, device="cuda")
+    rc = L.gm_mp_step(pm.handle, impl, 10, 400, 100, lib.ptr(idx), lib.ptr(idx), lib.ptr(idx), lib.ptr(idx), lib.ptr(ws),
+                      1024, lib.stream_ptr())
+    assert rc == 2 and "workspace too small" in L.gm_last_error().decode()          # GM_STATUS_WORKSPACE
+    nb = L.gm_forward_workspace_bytes(pm.handle, 400, 100, impl)
+    ws = torch.empty((nb,), dtype=torch.uint8, device="cuda")
+    rc = L.gm_mp_step(pm.handle, impl, 10, 400, 100, lib.ptr(idx), lib.ptr(idx), lib.ptr(idx), lib.ptr(idx), lib.ptr(ws),
+                      nb, lib.stream_ptr())
+    assert rc == 1 and "step=10" in L.gm_last_error().decode()                       # GM_STATUS_INVALID
+
+
+@pytest.mark.parametrize("impl,tol", [(1, ACC_TOL_SIMT), (2, ACC_TOL_TC)])
 @pytest.mark.parametrize("n,h", [(2000, 0.005), (2500, 0.012), (129, 0.005)])
 def test_forward_matches_oracle(gm, oracle_lib, impl, tol, n, h):
     ref, mine = seeded_models(gm, oracle_lib, seed=n)
