@@ -318,9 +318,11 @@ int wgrad(const StepCtx& c, const float* A, const float* B, bool edges, size_t w
 int mlp_tail_fwd(const StepCtx& c, const MlpRef& p, const Block& W2, const Block& W3, bool edges, const float* h1,
                  float* h2, float* z, float* xhat, float* rstd, float* y_out, const float* res_in, float* res_out) {
   TR(gemm(c, h1, W2.fwd, c.P + p.b2, nullptr, nullptr, nullptr, nullptr, nullptr, true, false, edges, h2));
-  TR(gemm(c, h2, W3.fwd, c.P + p.b3, nullptr, nullptr, nullptr, nullptr, nullptr, false, false, edges, z));
-  return tr_ln_fwd(z, c.P + p.g, c.P + p.b, edges ? c.E : c.N, edges ? c.E_dev : nullptr, xhat, rstd, y_out, res_in,
-                   res_out, c.st);
+  // layer 3 with the LayerNorm (+ residual) in its epilogue: the pre-normalisation rows z never go to memory
+  (void)z;
+  TrGemmArgs a{h2, nullptr, W3.fwd, c.P + p.b3, nullptr, nullptr, nullptr, nullptr, nullptr, y_out, 0, 0,
+               edges ? c.E : c.N, edges ? c.E_dev : nullptr, c.P + p.g, c.P + p.b, xhat, rstd, res_in, res_out};
+  return tr_gemm(a, c.st);
 }
 
 // ... and backward: dy (= d1 + d2[idx2]) -> dz3 -> dz2 -> dz1 (returned in dz_a), weight / bias / LayerNorm gradients

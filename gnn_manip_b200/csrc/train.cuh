@@ -28,6 +28,14 @@ struct TrGemmArgs {
   int accumulate;
   int M;
   const int* M_dev;
+  // LayerNorm epilogue (ln_g != null; excludes add1 / add2 / relu / mask / accumulate): z = acc + bias is normalised
+  // per row, xhat / rstd saved (optional), out (optional) = xhat * g + b, res_out (optional) = res_in + out
+  const float* ln_g;
+  const float* ln_b;
+  float* ln_xhat;
+  float* ln_rstd;
+  const float* res_in;
+  float* res_out;
 };
 int tr_gemm(const TrGemmArgs& a, cudaStream_t stream);
 

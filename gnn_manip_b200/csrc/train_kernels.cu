@@ -56,6 +56,12 @@ __device__ __forceinline__ void issue_gemm_kk(uint32_t a_s, uint32_t w_s, uint32
   }
 }
 
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
 __device__ __forceinline__ void prefetch_l2_line(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // Two tile slots per CTA (256 threads each, named barriers): the weights are shared, every slot has its own 64 KB
@@ -65,6 +71,9 @@ __device__ __forceinline__ void prefetch_l2_line(const void* p) { asm volatile("
 constexpr int kGemmSlots = 2;
 constexpr int kGemmThreads = kGemmSlots * kNT;
 
+// kLN: the epilogue is LayerNorm (+ residual) instead of adds / ReLU / mask: with a whole row per warp the statistics are
+// two warp reductions (same arithmetic as tr_ln_fwd_kernel), and the pre-normalisation rows never go to memory.
+template <bool kLN>
 __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) {
   extern __shared__ char smem_raw[];
   char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -134,8 +143,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
         const size_t off = (size_t)r * kTrH + 32 * (lane & 3);
         if (nt < n_tiles && a.in_idx == nullptr && nt * kT + r < M) prefetch_l2_line(a.x + (size_t)nt * kT * kTrH + off);
         if (r < rows_valid) {
-          if (a.mask) prefetch_l2_line(a.mask + (size_t)row0 * kTrH + off);
-          if (a.accumulate) prefetch_l2_line(a.out + (size_t)row0 * kTrH + off);
+          if (!kLN && a.mask) prefetch_l2_line(a.mask + (size_t)row0 * kTrH + off);
+          if (!kLN && a.accumulate) prefetch_l2_line(a.out + (size_t)row0 * kTrH + off);
+          if (kLN && a.res_out) prefetch_l2_line(a.res_in + (size_t)row0 * kTrH + off);
         }
       }
     }
@@ -151,8 +161,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
     w_ready = true;
     __syncwarp();
     // source rows of the gathered adds for this warp's 16 rows (lane i < 16: row i), fetched under the MMAs
-    int my_i1, my_i2;
-    {
+    int my_i1 = 0, my_i2 = 0;
+    if constexpr (!kLN) {
       const int rr = warp * R + (lane & 15);
       const bool rv = rr < rows_valid;
       my_i1 = (a.idx1 && rv) ? __ldg(a.idx1 + row0 + rr) : row0 + rr;
@@ -180,6 +190,39 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
     named_bar_sync(1 + slot, kNT);
     // ---- row-wise epilogue: every global access is one coalesced 512 B row; four rows per step with all their
     //      loads (gathered adds, mask, accumulate target) issued before the first use ----
+    if constexpr (kLN) {
+      const float4 gg = reinterpret_cast<const float4*>(a.ln_g)[lane], bb = reinterpret_cast<const float4*>(a.ln_b)[lane];
+#pragma unroll 1
+      for (int i0 = 0; i0 < R; i0 += 4) {
+        float4 ee[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = warp * R + i0 + i;
+          ee[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (a.res_out && r < rows_valid) ee[i] = __ldg(reinterpret_cast<const float4*>(a.res_in + (size_t)(row0 + r) * kTrH) + lane);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = warp * R + i0 + i;
+          if (r < rows_valid) {                    // (warp-uniform)
+            const size_t gr = (size_t)(row0 + r);
+            const float4 x = *reinterpret_cast<const float4*>(T + stg_off(r, 4 * lane));
+            const float mean = warp_sum((x.x + x.y) + (x.z + x.w)) * (1.0f / kTrH);
+            const float4 d = make_float4(x.x - mean, x.y - mean, x.z - mean, x.w - mean);
+            const float var = warp_sum(fmaf(d.x, d.x, fmaf(d.y, d.y, fmaf(d.z, d.z, d.w * d.w)))) * (1.0f / kTrH);
+            const float rstd = 1.0f / sqrtf(var + 1e-5f);
+            const float4 xh = make_float4(d.x * rstd, d.y * rstd, d.z * rstd, d.w * rstd);
+            if (a.ln_xhat) reinterpret_cast<float4*>(a.ln_xhat + gr * kTrH)[lane] = xh;
+            if (a.ln_rstd && lane == 0) a.ln_rstd[gr] = rstd;
+            const float4 y = make_float4(xh.x * gg.x + bb.x, xh.y * gg.y + bb.y, xh.z * gg.z + bb.z, xh.w * gg.w + bb.w);
+            if (a.out) reinterpret_cast<float4*>(a.out + gr * kTrH)[lane] = y;
+            if (a.res_out)
+              reinterpret_cast<float4*>(a.res_out + gr * kTrH)[lane] =
+                  make_float4(ee[i].x + y.x, ee[i].y + y.y, ee[i].z + y.z, ee[i].w + y.w);
+          }
+        }
+      }
+    } else {
 #pragma unroll 1
     for (int i0 = 0; i0 < R; i0 += 4) {
       float4 t1[4], t2[4], mk[4], oo[4];
@@ -211,6 +254,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
           *(reinterpret_cast<float4*>(a.out + (size_t)(row0 + r) * kTrH) + lane) = v;
         }
       }
+    }
     }
     named_bar_sync(1 + slot, kNT);             // the buffer is rewritten by the slot's next tile
   }
@@ -402,16 +446,22 @@ __global__ void tr_wgrad_reduce_kernel(const float* __restrict__ partial, int n_
 }  // namespace
 
 int tr_gemm(const TrGemmArgs& a, cudaStream_t stream) {
-  GM_REQUIRE(a.x != nullptr && a.chunk != nullptr && a.out != nullptr, "tr_gemm: NULL argument");
+  const bool ln = a.ln_g != nullptr;
+  GM_REQUIRE(a.x != nullptr && a.chunk != nullptr && (a.out != nullptr || ln), "tr_gemm: NULL argument");
+  GM_REQUIRE(!ln || (a.ln_b != nullptr && !a.add1 && !a.add2 && !a.mask && !a.relu && !a.accumulate),
+             "tr_gemm: the LayerNorm epilogue excludes adds / ReLU / mask / accumulate");
+  GM_REQUIRE(!ln || a.res_out == nullptr || a.res_in != nullptr, "tr_gemm: res_out needs res_in");
   if (a.M <= 0) return GM_OK;
   static PerDeviceOnce once;
   const int dev = once.begin();
   if (dev >= 0) {
-    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
     once.finish(dev);
   }
   const int grid = min(ceil_div(a.M, kT), kNumSMs);
-  tr_gemm_kernel<<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
+  if (ln) tr_gemm_kernel<true><<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
+  else tr_gemm_kernel<false><<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("tr_gemm_kernel");
   return GM_OK;
@@ -460,11 +510,6 @@ namespace {
 constexpr int kLnWarps = 8;                    // rows per block in the row kernels (warp per row)
 constexpr int kLnRowsPerBlock = 64;            // ln_bwd: rows a block walks (its dgamma / dbeta partial)
 
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
 
 // torch.nn.LayerNorm(128, eps=1e-5): biased variance, two-pass
 __global__ void __launch_bounds__(kLnWarps * 32)
