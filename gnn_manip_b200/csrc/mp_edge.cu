@@ -781,6 +781,49 @@ __device__ __forceinline__ void stage16_gather(uint32_t S_s, uint32_t db_base, u
   }
   cp_async_commit();
 }
+// ---- packed fp32 arithmetic (FADD2 / FMUL2 / FFMA2: two IEEE-rn operations per issued instruction; each half is
+// bit-identical to the scalar op) for the elementwise parts of the epilogues ----
+__device__ __forceinline__ float2 f2_add(float2 a, float2 b) {
+  float2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<unsigned long long&>(d))
+      : "l"(reinterpret_cast<unsigned long long&>(a)), "l"(reinterpret_cast<unsigned long long&>(b)));
+  return d;
+}
+__device__ __forceinline__ float2 f2_sub(float2 a, float2 b) {
+  float2 d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<unsigned long long&>(d))
+      : "l"(reinterpret_cast<unsigned long long&>(a)), "l"(reinterpret_cast<unsigned long long&>(b)));
+  return d;
+}
+__device__ __forceinline__ float2 f2_mul(float2 a, float2 b) {
+  float2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<unsigned long long&>(d))
+      : "l"(reinterpret_cast<unsigned long long&>(a)), "l"(reinterpret_cast<unsigned long long&>(b)));
+  return d;
+}
+__device__ __forceinline__ float2 f2_fma(float2 a, float2 b, float2 c) {
+  float2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(reinterpret_cast<unsigned long long&>(d))
+      : "l"(reinterpret_cast<unsigned long long&>(a)), "l"(reinterpret_cast<unsigned long long&>(b)),
+        "l"(reinterpret_cast<unsigned long long&>(c)));
+  return d;
+}
+__device__ __forceinline__ float2 f2_relu(float2 a) { return make_float2(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f)); }
+// bf16 hi / lo split of a pair (same values as split_bf16x2, the residual as one packed subtraction)
+__device__ __forceinline__ void split_pair(float2 x, uint32_t& hi, uint32_t& lo) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(x.x, x.y);
+  hi = *reinterpret_cast<uint32_t*>(&h);
+  const float2 r = f2_sub(x, make_float2(__uint_as_float(hi << 16), __uint_as_float(hi & 0xFFFF0000u)));
+  __nv_bfloat162 l = __floats2bfloat162_rn(r.x, r.y);
+  lo = *reinterpret_cast<uint32_t*>(&l);
+}
+__device__ __forceinline__ void put_operand32_inplace_p(const float2* v, uint32_t tR, int c32) {
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) split_pair(v[j], hi[j], lo[j]);
+  tmem_st16(tR + c32 * 32, hi);
+  tmem_st16(tR + c32 * 32 + 16, lo);
+}
 }  // namespace
 
 __global__ void __launch_bounds__(kNTE16, 1) mp_edge16_kernel(TcMlp m, TcGraph g, TcBuffers b) {
@@ -918,13 +961,13 @@ __global__ void __launch_bounds__(kNTE16, 1) mp_edge16_kernel(TcMlp m, TcGraph g
     };
     int cur_recv = -1;
     auto box_to_operand = [&](int c, uint32_t tR) {
-      float v[32];
+      float2 v[16];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float4 t = *reinterpret_cast<const float4*>(S + c * kBoxBytes + RO16(j));
-        v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+        v[2 * j] = make_float2(t.x, t.y); v[2 * j + 1] = make_float2(t.z, t.w);
       }
-      put_operand32_inplace(v, tR, c);
+      put_operand32_inplace_p(v, tR, c);
     };
     // e rows of a tile (landed in this warp's staging bytes) -> bf16 hi / lo operand of layer 1 in TMEM
     auto operand_from_stage = [&]() {
@@ -982,28 +1025,26 @@ __global__ void __launch_bounds__(kNTE16, 1) mp_edge16_kernel(TcMlp m, TcGraph g
       tc_fence_after();
       GM_ESTAMP(2);
       {
-        float va[32];
+        float2 va[16];
         float4 p[8];
         auto load_pr = [&](int c) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) p[j] = __ldg(reinterpret_cast<const float4*>(pr_row + c * 32) + j);
         };
-        auto e1_block = [&](int c, float* v) {
+        auto e1_block = [&](int c, float2* v) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float4 s4 = *reinterpret_cast<const float4*>(S + c * kBoxBytes + RO16(j));
-            v[4 * j] = fmaxf(v[4 * j] + (p[j].x + s4.x), 0.f);
-            v[4 * j + 1] = fmaxf(v[4 * j + 1] + (p[j].y + s4.y), 0.f);
-            v[4 * j + 2] = fmaxf(v[4 * j + 2] + (p[j].z + s4.z), 0.f);
-            v[4 * j + 3] = fmaxf(v[4 * j + 3] + (p[j].w + s4.w), 0.f);
+            v[2 * j] = f2_relu(f2_add(v[2 * j], f2_add(make_float2(p[j].x, p[j].y), make_float2(s4.x, s4.y))));
+            v[2 * j + 1] = f2_relu(f2_add(v[2 * j + 1], f2_add(make_float2(p[j].z, p[j].w), make_float2(s4.z, s4.w))));
           }
-          put_operand32_inplace(v, tY, c);
+          put_operand32_inplace_p(v, tY, c);
         };
-        tmem_ld32(tY + 32 * c0, va);
+        tmem_ld32(tY + 32 * c0, reinterpret_cast<float*>(va));
         load_pr(c0);
         tmem_ld_wait();
         e1_block(c0, va);
-        tmem_ld32(tY + 32 * c1, va);
+        tmem_ld32(tY + 32 * c1, reinterpret_cast<float*>(va));
         load_pr(c1);
         publish_half(0);
         tmem_ld_wait();
@@ -1019,24 +1060,22 @@ __global__ void __launch_bounds__(kNTE16, 1) mp_edge16_kernel(TcMlp m, TcGraph g
       tc_fence_after();
       GM_ESTAMP(4);
       {
-        float va[32];
-        auto e2_block = [&](int c, float* v) {
+        float2 va[16];
+        auto e2_block = [&](int c, float2* v) {
           float4 bs[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) bs[j] = GM_PRM4(prm + kOffB2 + c * 32 + 4 * j);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            v[4 * j] = fmaxf(v[4 * j] + bs[j].x, 0.f);
-            v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs[j].y, 0.f);
-            v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs[j].z, 0.f);
-            v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs[j].w, 0.f);
+            v[2 * j] = f2_relu(f2_add(v[2 * j], make_float2(bs[j].x, bs[j].y)));
+            v[2 * j + 1] = f2_relu(f2_add(v[2 * j + 1], make_float2(bs[j].z, bs[j].w)));
           }
-          put_operand32_inplace(v, tX, c);
+          put_operand32_inplace_p(v, tX, c);
         };
-        tmem_ld32(tX + 32 * c0, va);
+        tmem_ld32(tX + 32 * c0, reinterpret_cast<float*>(va));
         tmem_ld_wait();
         e2_block(c0, va);
-        tmem_ld32(tX + 32 * c1, va);
+        tmem_ld32(tX + 32 * c1, reinterpret_cast<float*>(va));
         publish_half(0);
         tmem_ld_wait();
         e2_block(c1, va);
@@ -1058,26 +1097,30 @@ __global__ void __launch_bounds__(kNTE16, 1) mp_edge16_kernel(TcMlp m, TcGraph g
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
           const int c = cc ? c1 : c0;
-          float x[32];
-          tmem_ld32(tY + 32 * c, x);
+          float2 x[16];
+          tmem_ld32(tY + 32 * c, reinterpret_cast<float*>(x));
           float4 t[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) t[j] = GM_PRM4(prm + kOffB3 + c * 32 + 4 * j);
           tmem_ld_wait();
-          float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
+          float2 sab = make_float2(0.f, 0.f), scd = sab;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            x[4 * j] += t[j].x; x[4 * j + 1] += t[j].y; x[4 * j + 2] += t[j].z; x[4 * j + 3] += t[j].w;
-            sa += x[4 * j]; sb += x[4 * j + 1]; sc += x[4 * j + 2]; sd += x[4 * j + 3];
+            x[2 * j] = f2_add(x[2 * j], make_float2(t[j].x, t[j].y));
+            x[2 * j + 1] = f2_add(x[2 * j + 1], make_float2(t[j].z, t[j].w));
+            sab = f2_add(sab, x[2 * j]);
+            scd = f2_add(scd, x[2 * j + 1]);
           }
-          const float sum_c = (sa + sb) + (sc + sd), mean_c = sum_c * (1.0f / 32.0f);
-          float qa = 0.f, qb = 0.f, qc = 0.f, qd = 0.f;
+          const float sum_c = (sab.x + sab.y) + (scd.x + scd.y), mean_c = sum_c * (1.0f / 32.0f);
+          const float2 mc2 = make_float2(mean_c, mean_c);
+          float2 qab = make_float2(0.f, 0.f), qcd = qab;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float u0 = x[4 * j] - mean_c, u1 = x[4 * j + 1] - mean_c, u2 = x[4 * j + 2] - mean_c, u3 = x[4 * j + 3] - mean_c;
-            qa = fmaf(u0, u0, qa); qb = fmaf(u1, u1, qb); qc = fmaf(u2, u2, qc); qd = fmaf(u3, u3, qd);
+            const float2 u01 = f2_sub(x[2 * j], mc2), u23 = f2_sub(x[2 * j + 1], mc2);
+            qab = f2_fma(u01, u01, qab);
+            qcd = f2_fma(u23, u23, qcd);
           }
-          const float m2_c = (qa + qb) + (qc + qd);
+          const float m2_c = (qab.x + qab.y) + (qcd.x + qcd.y);
           if (cc == 0) {
             sum_h = sum_c; m2_h = m2_c; mean_c0 = mean_c;
           } else {
@@ -1102,12 +1145,13 @@ __global__ void __launch_bounds__(kNTE16, 1) mp_edge16_kernel(TcMlp m, TcGraph g
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
           const int c = cc ? c1 : c0;
-          float x[32];
-          tmem_ld32(tY + 32 * c, x);
+          float2 x[16];
+          tmem_ld32(tY + 32 * c, reinterpret_cast<float*>(x));
           float4 t[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) t[j] = GM_PRM4(prm + kOffB3 + c * 32 + 4 * j);
           tmem_ld_wait();
+          const float2 mean2 = make_float2(mean, mean), rstd2 = make_float2(rstd, rstd);
           // the accumulator has been read for the last time and the next tile's layer-1 operand is in TMEM: its
           // GEMM 1 runs under the residual / segmented-sum phases of this tile
           if (cc == 1 && has_next) publish_both();
@@ -1115,11 +1159,12 @@ __global__ void __launch_bounds__(kNTE16, 1) mp_edge16_kernel(TcMlp m, TcGraph g
           for (int j = 0; j < 8; ++j) {
             const float4 g4 = GM_PRM4(prm + kOffG + c * 32 + 4 * j);
             const float4 b4 = GM_PRM4(prm + kOffBeta + c * 32 + 4 * j);
-            *reinterpret_cast<float4*>(S + c * kBoxBytes + RO16(j)) =
-                make_float4(((x[4 * j] + t[j].x) - mean) * rstd * g4.x + b4.x,
-                            ((x[4 * j + 1] + t[j].y) - mean) * rstd * g4.y + b4.y,
-                            ((x[4 * j + 2] + t[j].z) - mean) * rstd * g4.z + b4.z,
-                            ((x[4 * j + 3] + t[j].w) - mean) * rstd * g4.w + b4.w);
+            // ((x + b3) - mean) * rstd * g + beta, the last two as one fused multiply-add (as the scalar code compiles)
+            const float2 y01 = f2_fma(f2_mul(f2_sub(f2_add(x[2 * j], make_float2(t[j].x, t[j].y)), mean2), rstd2),
+                                      make_float2(g4.x, g4.y), make_float2(b4.x, b4.y));
+            const float2 y23 = f2_fma(f2_mul(f2_sub(f2_add(x[2 * j + 1], make_float2(t[j].z, t[j].w)), mean2), rstd2),
+                                      make_float2(g4.z, g4.w), make_float2(b4.z, b4.w));
+            *reinterpret_cast<float4*>(S + c * kBoxBytes + RO16(j)) = make_float4(y01.x, y01.y, y23.x, y23.y);
           }
         }
       }
