@@ -47,7 +47,8 @@ def _worker(rank, world, port, q):
     local = torch.randn((total,), generator=g)
     one = average_gradients(local.clone())
     per_bucket = average_gradients(local.clone(), buckets)
-    q.put((rank, local, one, per_bucket))
+    # numpy arrays travel by value; torch tensors would be handed over as file descriptors, which needs this process alive
+    q.put((rank, local.numpy(), one.numpy(), per_bucket.numpy()))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -62,7 +63,7 @@ def test_average_gradients_gloo_world2():
     got = {}
     for _ in range(2):
         rank, local, one, per_bucket = q.get(timeout=180)
-        got[rank] = (local.clone(), one.clone(), per_bucket.clone())
+        got[rank] = (torch.from_numpy(local), torch.from_numpy(one), torch.from_numpy(per_bucket))
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
