@@ -832,7 +832,9 @@ __global__ void __launch_bounds__(kNTE16, 1) mp_edge16_kernel(TcMlp m, TcGraph g
   const uint32_t W_s = smem_u32(base);
   char* S_base = base + kWBytes;
   EdgeShared* sh = reinterpret_cast<EdgeShared*>(S_base + 2 * kStageBytes);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // (the shuffle tells the compiler that the warp index is warp-uniform: role branches become uniform branches and the
+  // uniform datapath stays usable inside them -- without it every global access re-creates its descriptor with R2UR)
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const uint32_t rank = cluster_ctarank();     // 0: leader (issues the pair's MMAs), 1: peer
   if (tid == 0 && (W_s & 1023u) != 0u) {
     printf("gnn_manip_b200: mp_edge16 dynamic shared memory is not 1024-byte aligned\n");
