@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(kNTE3, 1) mp_edge_kernel(TcMlp m, TcGraph g, T
   const uint32_t W_s = smem_u32(base);
   char* S_base = base + kWBytes;
   EdgeShared* sh = reinterpret_cast<EdgeShared*>(S_base + 2 * kStageBytes);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // (warp-uniform)
   const uint32_t rank = cluster_ctarank();     // 0: leader (issues the pair's MMAs), 1: peer
   if (tid == 0 && (W_s & 1023u) != 0u) {
     printf("gnn_manip_b200: mp_edge dynamic shared memory is not 1024-byte aligned\n");
@@ -1282,7 +1282,7 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
   float* b1s = reinterpret_cast<float*>(base + 2 * kWLayer + kH * 16);  // [128]
   char* S_base = base + kWBytes;
   EdgeShared* sh = reinterpret_cast<EdgeShared*>(S_base + 2 * kStageBytes);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // (warp-uniform)
   const uint32_t rank = cluster_ctarank();
   if (tid == 0) {
     mbar_init(smem_u32(&sh->w_full), 1);
@@ -1476,7 +1476,7 @@ selftest_gemm_ts_kernel(const float* __restrict__ x, const void* chunk, float* _
   const uint32_t W_s = smem_u32(base);
   char* S = base + kChunkBytes;
   EdgeShared* sh = reinterpret_cast<EdgeShared*>(S + kStageBytes);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // (warp-uniform)
   const uint32_t bar_w = smem_u32(&sh->w_full), bar_d = smem_u32(&sh->d_ready[0]);
   if (tid == 0) {
     mbar_init(bar_w, 1);

@@ -182,7 +182,8 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
   c.A0 = base; c.T = base + kChunkBytes; c.W = base + 2 * kChunkBytes;
   c.a0_s = smem_u32(c.A0); c.t_s = smem_u32(c.T); c.w_s = smem_u32(c.W);
   c.misc = reinterpret_cast<Misc16*>(base + 3 * kChunkBytes);
-  c.tid = threadIdx.x; c.lane = c.tid & 31; c.warp = c.tid >> 5; c.q = c.warp & 3; c.cq = c.warp >> 2;
+  c.tid = threadIdx.x; c.lane = c.tid & 31; c.warp = __shfl_sync(0xffffffffu, c.tid >> 5, 0);   // (provably warp-uniform: see mp_edge16_kernel)
+  c.q = c.warp & 3; c.cq = c.warp >> 2;
   c.row = c.q * 32 + c.lane;
   c.col0 = c.cq * 32;
   c.bar_w = smem_u32(&c.misc->bar_w);

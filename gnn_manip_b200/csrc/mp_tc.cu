@@ -60,7 +60,7 @@ struct Ctx {
 __device__ __forceinline__ void ctx_init(Ctx& c, char* smem, int n_a, int tmem_cols) {
   c.tid = threadIdx.x;
   c.lane = c.tid & 31;
-  c.warp = c.tid >> 5;
+  c.warp = __shfl_sync(0xffffffffu, c.tid >> 5, 0);   // (provably warp-uniform: see mp_edge16_kernel)
   c.q = c.warp & 3;
   c.hf = c.warp >> 2;
   c.row = c.q * 32 + c.lane;
