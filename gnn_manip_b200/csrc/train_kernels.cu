@@ -73,8 +73,13 @@ constexpr int kGemmThreads = kGemmSlots * kNT;
 
 // kLN: the epilogue is LayerNorm (+ residual) instead of adds / ReLU / mask: with a whole row per warp the statistics are
 // two warp reductions (same arithmetic as tr_ln_fwd_kernel), and the pre-normalisation rows never go to memory.
-template <bool kLN>
+// kMode specialises the row epilogue at compile time (the generic version carries the predicated code of every option):
+// 0 = any combination (run-time flags), 1 = neither adds, mask nor accumulate, 2 = mask only, 3 = accumulate only.
+template <bool kLN, int kMode>
 __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) {
+  const bool has_add1 = kMode == 0 && a.add1 != nullptr, has_add2 = kMode == 0 && a.add2 != nullptr;
+  const bool has_mask = kMode == 2 || (kMode == 0 && a.mask != nullptr);
+  const bool has_acc = kMode == 3 || (kMode == 0 && a.accumulate != 0);
   extern __shared__ char smem_raw[];
   char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   char* W = base;                              // weight images (hi, lo), resident
@@ -143,8 +148,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
         const size_t off = (size_t)r * kTrH + 32 * (lane & 3);
         if (nt < n_tiles && a.in_idx == nullptr && nt * kT + r < M) prefetch_l2_line(a.x + (size_t)nt * kT * kTrH + off);
         if (r < rows_valid) {
-          if (!kLN && a.mask) prefetch_l2_line(a.mask + (size_t)row0 * kTrH + off);
-          if (!kLN && a.accumulate) prefetch_l2_line(a.out + (size_t)row0 * kTrH + off);
+          if (!kLN && has_mask) prefetch_l2_line(a.mask + (size_t)row0 * kTrH + off);
+          if (!kLN && has_acc) prefetch_l2_line(a.out + (size_t)row0 * kTrH + off);
           if (kLN && a.res_out) prefetch_l2_line(a.res_in + (size_t)row0 * kTrH + off);
         }
       }
@@ -162,7 +167,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
     __syncwarp();
     // source rows of the gathered adds for this warp's 16 rows (lane i < 16: row i), fetched under the MMAs
     int my_i1 = 0, my_i2 = 0;
-    if constexpr (!kLN) {
+    if constexpr (!kLN && kMode == 0) {
       const int rr = warp * R + (lane & 15);
       const bool rv = rr < rows_valid;
       my_i1 = (a.idx1 && rv) ? __ldg(a.idx1 + row0 + rr) : row0 + rr;
@@ -231,26 +236,27 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
         const int r = warp * R + i0 + i;
         const bool ok = r < rows_valid;
         const size_t gr = (size_t)(row0 + r);
-        const int s1 = __shfl_sync(0xffffffffu, my_i1, i0 + i), s2 = __shfl_sync(0xffffffffu, my_i2, i0 + i);
+        int s1 = 0, s2 = 0;
+        if constexpr (kMode == 0) { s1 = __shfl_sync(0xffffffffu, my_i1, i0 + i); s2 = __shfl_sync(0xffffffffu, my_i2, i0 + i); }
         t1[i] = t2[i] = mk[i] = oo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (a.add1 && ok) t1[i] = __ldg(reinterpret_cast<const float4*>(a.add1 + (size_t)s1 * kTrH) + lane);
-        if (a.add2 && ok) t2[i] = __ldg(reinterpret_cast<const float4*>(a.add2 + (size_t)s2 * kTrH) + lane);
-        if (a.mask && ok) mk[i] = __ldg(reinterpret_cast<const float4*>(a.mask + gr * kTrH) + lane);
-        if (a.accumulate && ok) oo[i] = *(reinterpret_cast<const float4*>(a.out + gr * kTrH) + lane);
+        if (has_add1 && ok) t1[i] = __ldg(reinterpret_cast<const float4*>(a.add1 + (size_t)s1 * kTrH) + lane);
+        if (has_add2 && ok) t2[i] = __ldg(reinterpret_cast<const float4*>(a.add2 + (size_t)s2 * kTrH) + lane);
+        if (has_mask && ok) mk[i] = __ldg(reinterpret_cast<const float4*>(a.mask + gr * kTrH) + lane);
+        if (has_acc && ok) oo[i] = *(reinterpret_cast<const float4*>(a.out + gr * kTrH) + lane);
       }
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int r = warp * R + i0 + i;
         if (r < rows_valid) {
           float4 v = *reinterpret_cast<const float4*>(T + stg_off(r, 4 * lane));
-          if (a.add1) { v.x += t1[i].x; v.y += t1[i].y; v.z += t1[i].z; v.w += t1[i].w; }
-          if (a.add2) { v.x += t2[i].x; v.y += t2[i].y; v.z += t2[i].z; v.w += t2[i].w; }
+          if (has_add1) { v.x += t1[i].x; v.y += t1[i].y; v.z += t1[i].z; v.w += t1[i].w; }
+          if (has_add2) { v.x += t2[i].x; v.y += t2[i].y; v.z += t2[i].z; v.w += t2[i].w; }
           if (a.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-          if (a.mask) {
+          if (has_mask) {
             v.x = mk[i].x > 0.f ? v.x : 0.f; v.y = mk[i].y > 0.f ? v.y : 0.f;
             v.z = mk[i].z > 0.f ? v.z : 0.f; v.w = mk[i].w > 0.f ? v.w : 0.f;
           }
-          if (a.accumulate) { v.x += oo[i].x; v.y += oo[i].y; v.z += oo[i].z; v.w += oo[i].w; }
+          if (has_acc) { v.x += oo[i].x; v.y += oo[i].y; v.z += oo[i].z; v.w += oo[i].w; }
           *(reinterpret_cast<float4*>(a.out + (size_t)(row0 + r) * kTrH) + lane) = v;
         }
       }
@@ -455,13 +461,20 @@ int tr_gemm(const TrGemmArgs& a, cudaStream_t stream) {
   static PerDeviceOnce once;
   const int dev = once.begin();
   if (dev >= 0) {
-    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
-    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    GM_CUDA(cudaFuncSetAttribute(tr_gemm_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
     once.finish(dev);
   }
   const int grid = min(ceil_div(a.M, kT), kNumSMs);
-  if (ln) tr_gemm_kernel<true><<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
-  else tr_gemm_kernel<false><<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
+  const bool adds = a.add1 != nullptr || a.add2 != nullptr, mask = a.mask != nullptr, acc = a.accumulate != 0;
+  if (ln) tr_gemm_kernel<true, 1><<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
+  else if (!adds && !mask && !acc) tr_gemm_kernel<false, 1><<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
+  else if (!adds && mask && !acc) tr_gemm_kernel<false, 2><<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
+  else if (!adds && !mask && acc) tr_gemm_kernel<false, 3><<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
+  else tr_gemm_kernel<false, 0><<<grid, kGemmThreads, kGemmSmem, stream>>>(a);
   GM_LAUNCHED(1);
   GM_LAUNCH_CHECK("tr_gemm_kernel");
   return GM_OK;
