@@ -84,8 +84,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
   char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   char* W = base;                              // weight images (hi, lo), resident
   GemmSmem* sh = reinterpret_cast<GemmSmem*>(base + (1 + kGemmSlots) * kTrChunkBytes);
-  const int slot = threadIdx.x / kNT, tid = threadIdx.x % kNT;
-  const int lane = tid & 31, warp = tid >> 5, q = warp & 3, hf = warp >> 2, row = q * 32 + lane;
+  // (slot through a shuffle: provably warp-uniform, so the tile loop is uniform control flow for the compiler)
+  const int slot = __shfl_sync(0xffffffffu, threadIdx.x / kNT, 0), tid = threadIdx.x % kNT;
+  const int lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), q = warp & 3, hf = warp >> 2, row = q * 32 + lane;
   char* A = base + (1 + slot) * kTrChunkBytes; // operand images (hi, lo) of this slot ...
   char* T = A;                                 // ... and, after the MMAs, its fp32 staging tile
   const uint32_t bar_w = smem_u32(&sh->bar_w), bar_mma = smem_u32(&sh->bar_mma[slot]);
@@ -119,12 +120,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
       float4 x[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
+        // branch-free: rows past the end re-read the tile's last valid row and are zeroed afterwards
         const int r = warp * R + i0 + i;
-        x[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < rows_valid) {
-          const size_t src = a.in_idx ? (size_t)a.in_idx[row0 + r] : (size_t)(row0 + r);
-          x[i] = __ldg(reinterpret_cast<const float4*>(a.x + src * kTrH) + lane);
-        }
+        size_t src = (size_t)(row0 + min(r, rows_valid - 1));
+        if (a.in_idx) src = (size_t)a.in_idx[src];
+        x[i] = __ldg(reinterpret_cast<const float4*>(a.x + src * kTrH) + lane);
+        if (r >= rows_valid) x[i] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -234,8 +235,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int r = warp * R + i0 + i;
-        const bool ok = r < rows_valid;
-        const size_t gr = (size_t)(row0 + r);
+        const bool ok = true;                      // (loads are clamped to the last valid row instead of branched around)
+        const size_t gr = (size_t)(row0 + min(r, rows_valid - 1));
         int s1 = 0, s2 = 0;
         if constexpr (kMode == 0) { s1 = __shfl_sync(0xffffffffu, my_i1, i0 + i); s2 = __shfl_sync(0xffffffffu, my_i2, i0 + i); }
         t1[i] = t2[i] = mk[i] = oo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -247,7 +248,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int r = warp * R + i0 + i;
-        if (r < rows_valid) {
+        {
           float4 v = *reinterpret_cast<const float4*>(T + stg_off(r, 4 * lane));
           if (has_add1) { v.x += t1[i].x; v.y += t1[i].y; v.z += t1[i].z; v.w += t1[i].w; }
           if (has_add2) { v.x += t2[i].x; v.y += t2[i].y; v.z += t2[i].z; v.w += t2[i].w; }
@@ -257,7 +258,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) tr_gemm_kernel(TrGemmArgs a) 
             v.z = mk[i].z > 0.f ? v.z : 0.f; v.w = mk[i].w > 0.f ? v.w : 0.f;
           }
           if (has_acc) { v.x += oo[i].x; v.y += oo[i].y; v.z += oo[i].z; v.w += oo[i].w; }
-          *(reinterpret_cast<float4*>(a.out + (size_t)(row0 + r) * kTrH) + lane) = v;
+          if (r < rows_valid) *(reinterpret_cast<float4*>(a.out + (size_t)(row0 + r) * kTrH) + lane) = v;
         }
       }
     }
