@@ -249,6 +249,12 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
   d |= (uint64_t)2 << 61;                    // layout type = SWIZZLE_128B
   return d;
 }
+// Descriptor of the operand `bytes` further on (bytes % 16 == 0): the start address sits in the low 14 bits in units of
+// 16 bytes and shared memory ends below 256 KB, so this is ONE 32-bit add on the low word -- the MMA-issuing thread's
+// instruction stream (not the tensor pipe) paces a chain of small MMAs, every instruction saved there shortens a GEMM.
+__device__ __forceinline__ uint64_t umma_desc_advance(uint64_t desc, uint32_t bytes) {
+  return desc + (uint64_t)(bytes >> 4);
+}
 // Instruction descriptor: kind::f16, A = B = BF16, D = F32, both K-major, M x N tile.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);

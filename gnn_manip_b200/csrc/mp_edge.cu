@@ -153,16 +153,17 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {   // arrives on
 }
 // one whole layer GEMM of a slot (24 MMAs): w_layer_s = this CTA's {Wh.k0, Wh.k1, Wl.k0, Wl.k1} blocks of the layer
 __device__ __forceinline__ void issue_layer_pair(uint32_t w_layer_s, uint32_t tD, uint32_t tAH, uint32_t tAL) {
+  const uint64_t w0 = umma_desc_sw128(w_layer_s);      // base descriptor once, one add per MMA (umma_desc_advance)
 #pragma unroll
   for (int p = 0; p < 4; ++p) {
-    const uint32_t wb = w_layer_s + p * kWBlock, kcol = (uint32_t)(p & 1) * 32u;
+    const uint32_t kcol = (uint32_t)(p & 1) * 32u;
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks)
-      umma_bf16_ts_pair(tD, tAH + kcol + ks * 8, umma_desc_sw128(wb + ks * 32), kIdescPair, (p | ks) ? 1u : 0u);
+      umma_bf16_ts_pair(tD, tAH + kcol + ks * 8, umma_desc_advance(w0, p * kWBlock + ks * 32), kIdescPair, (p | ks) ? 1u : 0u);
     if (p < 2) {
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks)
-        umma_bf16_ts_pair(tD, tAL + kcol + ks * 8, umma_desc_sw128(wb + ks * 32), kIdescPair, 1u);
+        umma_bf16_ts_pair(tD, tAL + kcol + ks * 8, umma_desc_advance(w0, p * kWBlock + ks * 32), kIdescPair, 1u);
     }
   }
 }
@@ -247,14 +248,16 @@ __device__ __forceinline__ void put_operand32_inplace(const float* v, uint32_t t
 }
 // the 12 MMAs of one K half (64 K elements) of a layer: A (in-place layout) from region tA, weights {Wh.k, Wl.k}
 __device__ __forceinline__ void issue_half_pair(uint32_t w_layer_s, uint32_t tD, uint32_t tA, int half) {
-  const uint32_t wh = w_layer_s + half * kWBlock, wl = w_layer_s + (2 + half) * kWBlock;
+  // base descriptors once, one add per MMA (umma_desc_advance)
+  const uint64_t dh = umma_desc_sw128(w_layer_s + half * kWBlock), dl = umma_desc_advance(dh, 2 * kWBlock);
+  const uint32_t a0 = tA + 64u * half;         // ks = 4 half + kk: column 32 (ks >> 1) + 8 (ks & 1)
 #pragma unroll
   for (int kk = 0; kk < 4; ++kk) {
-    const int ks = 4 * half + kk;
-    const uint32_t a_hi = tA + 32u * (ks >> 1) + 8u * (ks & 1), a_lo = a_hi + 16u;
-    umma_bf16_ts_pair(tD, a_hi, umma_desc_sw128(wh + kk * 32), kIdescPair, (half | kk) ? 1u : 0u);
-    umma_bf16_ts_pair(tD, a_lo, umma_desc_sw128(wh + kk * 32), kIdescPair, 1u);
-    umma_bf16_ts_pair(tD, a_hi, umma_desc_sw128(wl + kk * 32), kIdescPair, 1u);
+    const uint32_t a_hi = a0 + 32u * (kk >> 1) + 8u * (kk & 1), a_lo = a_hi + 16u;
+    const uint64_t bh = umma_desc_advance(dh, kk * 32), bl = umma_desc_advance(dl, kk * 32);
+    umma_bf16_ts_pair(tD, a_hi, bh, kIdescPair, (half | kk) ? 1u : 0u);
+    umma_bf16_ts_pair(tD, a_lo, bh, kIdescPair, 1u);
+    umma_bf16_ts_pair(tD, a_hi, bl, kIdescPair, 1u);
   }
 }
 

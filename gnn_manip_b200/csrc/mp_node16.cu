@@ -62,7 +62,7 @@ __device__ __forceinline__ void store_a8_16(char* a, int row, int col, const flo
 }
 
 __device__ __forceinline__ void load_w16(const Ctx16& c, const void* chunk) {
-  if (c.tid == 0) {
+  if (c.warp == 0 && c.lane == 0) {
     mbar_expect_tx(c.bar_w, kChunkBytes);
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -76,16 +76,17 @@ __device__ __forceinline__ void launch_gemm16(Ctx16& c, uint32_t a_s, bool accum
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
-  if (c.tid == 0) {
+  if (c.warp == 0 && c.lane == 0) {              // (warp-uniform test first: the MMAs are issued from uniform control flow)
     mbar_wait(c.bar_w, c.ph_w);
     tc_fence_after();
+    const uint64_t a0 = umma_desc_sw128(a_s), w0 = umma_desc_sw128(c.w_s);   // base descriptors once, one add per MMA operand
 #pragma unroll
     for (int kb = 0; kb < 2; ++kb) {
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks) {
         const uint32_t off = kb * kKBlockBytes + ks * 32;
-        const uint64_t ah = umma_desc_sw128(a_s + off), al = umma_desc_sw128(a_s + kImageBytes + off);
-        const uint64_t wh = umma_desc_sw128(c.w_s + off), wl = umma_desc_sw128(c.w_s + kImageBytes + off);
+        const uint64_t ah = umma_desc_advance(a0, off), al = umma_desc_advance(a0, kImageBytes + off);
+        const uint64_t wh = umma_desc_advance(w0, off), wl = umma_desc_advance(w0, kImageBytes + off);
         umma_bf16_ss(c.tmem, ah, wh, kIdesc16, (accumulate || kb || ks) ? 1u : 0u);
         umma_bf16_ss(c.tmem, ah, wl, kIdesc16, 1u);
         umma_bf16_ss(c.tmem, al, wh, kIdesc16, 1u);

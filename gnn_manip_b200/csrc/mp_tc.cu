@@ -112,13 +112,14 @@ __device__ __forceinline__ void load_w(const Ctx& c, const void* chunk) {
 
 // thread 0: D[tmem_d] (+)= A x W^T with the bf16x3 split; 8 K-steps x 3 products.
 __device__ __forceinline__ void issue_mma(uint32_t a_s, uint32_t w_s, uint32_t tmem_d, bool accumulate) {
+  const uint64_t a0 = umma_desc_sw128(a_s), w0 = umma_desc_sw128(w_s);   // base descriptors once, one add per MMA operand
 #pragma unroll
   for (int kb = 0; kb < 2; ++kb) {
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks) {
       const uint32_t off = kb * kKBlockBytes + ks * 32;
-      const uint64_t ah = umma_desc_sw128(a_s + off), al = umma_desc_sw128(a_s + kImageBytes + off);
-      const uint64_t wh = umma_desc_sw128(w_s + off), wl = umma_desc_sw128(w_s + kImageBytes + off);
+      const uint64_t ah = umma_desc_advance(a0, off), al = umma_desc_advance(a0, kImageBytes + off);
+      const uint64_t wh = umma_desc_advance(w0, off), wl = umma_desc_advance(w0, kImageBytes + off);
       umma_bf16_ss(tmem_d, ah, wh, kIdesc, (accumulate || kb || ks) ? 1u : 0u);
       umma_bf16_ss(tmem_d, ah, wl, kIdesc, 1u);
       umma_bf16_ss(tmem_d, al, wh, kIdesc, 1u);

@@ -42,13 +42,14 @@ struct GemmSmem {
 };
 
 __device__ __forceinline__ void issue_gemm_kk(uint32_t a_s, uint32_t w_s, uint32_t tmem_d) {
+  const uint64_t a0 = umma_desc_sw128(a_s), w0 = umma_desc_sw128(w_s);   // base descriptors once, one add per MMA operand
 #pragma unroll
   for (int kb = 0; kb < 2; ++kb) {
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks) {
       const uint32_t off = kb * kKBlock + ks * 32;
-      const uint64_t ah = umma_desc_sw128(a_s + off), al = umma_desc_sw128(a_s + kImage + off);
-      const uint64_t wh = umma_desc_sw128(w_s + off), wl = umma_desc_sw128(w_s + kImage + off);
+      const uint64_t ah = umma_desc_advance(a0, off), al = umma_desc_advance(a0, kImage + off);
+      const uint64_t wh = umma_desc_advance(w0, off), wl = umma_desc_advance(w0, kImage + off);
       umma_bf16_ss(tmem_d, ah, wh, kIdescKK, (kb | ks) ? 1u : 0u);
       umma_bf16_ss(tmem_d, ah, wl, kIdescKK, 1u);
       umma_bf16_ss(tmem_d, al, wh, kIdescKK, 1u);
