@@ -235,31 +235,39 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
       waited = true;
     }
     // ---- aggregate per node (first-tile partial + carries of the following 64-row blocks) -> A0 ----
-    {
-      float4 x[kR16];
-      int sb[kR16], se[kR16];
+    // Four rows at a time with every load issued before the first use: the partial row and the first two carries
+    // (a receiver's segment rarely spans more than three 64-row blocks) are independent predicated loads, not a
+    // data-dependent loop per row; summation order as before (partial, then the carries in block order).
 #pragma unroll
-      for (int i = 0; i < kR16; ++i) {
-        const int r = c.warp * kR16 + i;
-        sb[i] = __shfl_sync(0xffffffffu, rp, i);
-        se[i] = __shfl_sync(0xffffffffu, rp, i + 1);
-        x[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r >= rows_valid) se[i] = sb[i];
-        if (se[i] > sb[i]) x[i] = __ldg(reinterpret_cast<const float4*>(b.aggpart + (size_t)(node0 + r) * kH) + c.lane);
+    for (int i0 = 0; i0 < kR16; i0 += 4) {
+      float4 x[4], c1[4], c2[4];
+      int t0[4], t1[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = c.warp * kR16 + i0 + i;
+        const int sb = __shfl_sync(0xffffffffu, rp, i0 + i);
+        int se = __shfl_sync(0xffffffffu, rp, i0 + i + 1);
+        if (r >= rows_valid) se = sb;
+        const bool any = se > sb;
+        t0[i] = sb / kAggRows;
+        t1[i] = any ? (se - 1) / kAggRows : t0[i] - 1;      // t1 - t0 = number of carries; -1: no edges at all
+        x[i] = c1[i] = c2[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (any) x[i] = __ldg(reinterpret_cast<const float4*>(b.aggpart + (size_t)(node0 + r) * kH) + c.lane);
+        if (t1[i] >= t0[i] + 1) c1[i] = __ldg(reinterpret_cast<const float4*>(b.carry + (size_t)(t0[i] + 1) * kH) + c.lane);
+        if (t1[i] >= t0[i] + 2) c2[i] = __ldg(reinterpret_cast<const float4*>(b.carry + (size_t)(t0[i] + 2) * kH) + c.lane);
       }
 #pragma unroll
-      for (int i = 0; i < kR16; ++i) {
-        if (se[i] > sb[i]) {
-          const int t0 = sb[i] / kAggRows, t1 = (se[i] - 1) / kAggRows;
-          for (int t = t0 + 1; t <= t1; ++t) {
-            const float4 y = __ldg(reinterpret_cast<const float4*>(b.carry + (size_t)t * kH) + c.lane);
-            x[i].x += y.x; x[i].y += y.y; x[i].z += y.z; x[i].w += y.w;
-          }
+      for (int i = 0; i < 4; ++i) {
+        if (t1[i] >= t0[i] + 1) { x[i].x += c1[i].x; x[i].y += c1[i].y; x[i].z += c1[i].z; x[i].w += c1[i].w; }
+        if (t1[i] >= t0[i] + 2) { x[i].x += c2[i].x; x[i].y += c2[i].y; x[i].z += c2[i].z; x[i].w += c2[i].w; }
+        for (int t = t0[i] + 3; t <= t1[i]; ++t) {
+          const float4 y = __ldg(reinterpret_cast<const float4*>(b.carry + (size_t)t * kH) + c.lane);
+          x[i].x += y.x; x[i].y += y.y; x[i].z += y.z; x[i].w += y.w;
         }
         uint2 hi, lo;
         split_bf16x2(x[i].x, x[i].y, hi.x, lo.x);
         split_bf16x2(x[i].z, x[i].w, hi.y, lo.y);
-        const uint32_t o = a_off16(c.warp * kR16 + i, 4 * c.lane);
+        const uint32_t o = a_off16(c.warp * kR16 + i0 + i, 4 * c.lane);
         *reinterpret_cast<uint2*>(c.A0 + o) = hi;
         *reinterpret_cast<uint2*>(c.A0 + kImageBytes + o) = lo;
       }
