@@ -171,6 +171,14 @@ __device__ __forceinline__ void acc_to_stage16(const Ctx16& c, const float* __re
     *reinterpret_cast<float4*>(c.T + s_off16(c.row, c.col0 + 4 * j)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
 }
 
+#ifdef GM_STAMPS
+// Debug aid (-DGM_STAMPS): thread 0 of CTA 0 records clock64() along its first tile; gm_debug_stamps() entries 32..55
+__device__ unsigned long long g_n16_stamps[24];
+#define GM_N16(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_n16_stamps[i] = clock64(); } while (0)
+#else
+#define GM_N16(i) do { } while (0)
+#endif
+
 }  // namespace
 
 // chunks: m.wc[0] = W1[:, 0:128] (aggregated edges), m.wc[1] = W1[:, 128:256] (node), m.wc[2], m.wc[3];
@@ -214,6 +222,7 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
   tc_fence_after();
   c.tmem = c.misc->tmem_base;
 
+  GM_N16(0);
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
   bool waited = false;
   if ((int)blockIdx.x < n_tiles) load_w16(c, m.wc[1]);
@@ -225,15 +234,19 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
       const float* v_in = b.v;
       rows_to_a16(c, c.T, rows_valid, [=](int r) { return v_in + (size_t)(node0 + r) * kH; });
     }
+    GM_N16(1);
     launch_gemm16(c, c.t_s, false);
+    GM_N16(2);
     const int rp = __ldg(g.recv_ptr + min(node0 + c.warp * kR16 + min(c.lane, kR16), g.n_nodes));
     wait_gemm16(c);
+    GM_N16(3);
     load_w16(c, m.wc[0]);
     if (!waited) {
       pdl_wait();                                  // aggpart / carry of this step's edge kernel are complete from here on
       pdl_launch_dependents();
       waited = true;
     }
+    GM_N16(4);
     // ---- aggregate per node (first-tile partial + carries of the following 64-row blocks) -> A0 ----
     // Four rows at a time with every load issued before the first use: the partial row and the first two carries
     // (a receiver's segment rarely spans more than three 64-row blocks) are independent predicated loads, not a
@@ -272,8 +285,11 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
         *reinterpret_cast<uint2*>(c.A0 + kImageBytes + o) = lo;
       }
     }
+    GM_N16(5);
     launch_gemm16(c, c.a0_s, true);                // D += agg W1a^T
+    GM_N16(6);
     wait_gemm16(c);
+    GM_N16(7);
     load_w16(c, m.wc[2]);
     {                                              // T is free: the fp32 residual rows travel into it meanwhile
       const float* v_in = b.v;
@@ -286,13 +302,19 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
       cp_async_commit();
     }
     epi_hidden16(c, prm + kQB1);
+    GM_N16(8);
     launch_gemm16(c, c.a0_s, false);               // layer 2
+    GM_N16(9);
     wait_gemm16(c);
+    GM_N16(10);
     load_w16(c, m.wc[3]);
     epi_hidden16(c, prm + kQB2);
     cp_async_wait_all();
+    GM_N16(11);
     launch_gemm16(c, c.a0_s, false);               // layer 3 (its barrier also publishes the residual rows in T)
+    GM_N16(12);
     wait_gemm16(c);
+    GM_N16(13);
     load_w16(c, has_dec ? next.wc[0] : next.wc[3]);
     // ---- LayerNorm + residual: v' -> T (fp32) and A0 (operand) ----
     {
@@ -333,21 +355,30 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
 #pragma unroll
       for (int g8 = 0; g8 < 4; ++g8) store_a8_16(c.A0, c.row, c.col0 + 8 * g8, x + 8 * g8);
     }
+    GM_N16(14);
     launch_gemm16(c, c.a0_s, false);               // v' Wr^T   |   decoder layer 1
+    GM_N16(15);
     stage_out16(c, b.v, node0, rows_valid);        // v' rows leave while the GEMM runs
+    GM_N16(16);
     wait_gemm16(c);
+    GM_N16(17);
     if (!has_dec) {
       load_w16(c, next.wc[4]);
       __syncthreads();                             // every warp is done reading v' out of T
       acc_to_stage16(c, next.b1);                  // Pr carries b1 of the next edge MLP (mp_edge.cu adds no bias)
+      GM_N16(18);
       launch_gemm16(c, c.a0_s, false);             // v' Ws^T (the barrier inside publishes T)
+      GM_N16(19);
       stage_out16(c, b.pr, node0, rows_valid);
       wait_gemm16(c);
+      GM_N16(20);
       __syncthreads();
       acc_to_stage16(c, nullptr);
       tc_fence_before();
       __syncthreads();
+      GM_N16(21);
       stage_out16(c, b.ps, node0, rows_valid);
+      GM_N16(22);
     } else {
       // decoder: Linear+ReLU, Linear+ReLU on the tensor cores, Linear(128 -> out_dim) on CUDA cores (epd_gnn.py:49, 96)
       load_w16(c, next.wc[1]);
@@ -387,6 +418,15 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
   tc_fence_before();
   __syncthreads();
   if (c.warp == 0) tmem_dealloc(c.tmem, 128);
+}
+
+int tc_debug_stamps_node16(unsigned long long* out_host, int n) {
+#ifdef GM_STAMPS
+  if (n >= 56) GM_CUDA(cudaMemcpyFromSymbol(out_host + 32, g_n16_stamps, sizeof(unsigned long long) * 24));
+#else
+  (void)out_host; (void)n;
+#endif
+  return GM_OK;
 }
 
 int tc_configure_node16() {

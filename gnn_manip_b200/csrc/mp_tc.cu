@@ -845,6 +845,7 @@ int tc_configure() {
 int tc_debug_stamps(unsigned long long* out_host, int n) {
 #ifdef GM_STAMPS
   GM_CUDA(cudaMemcpyFromSymbol(out_host, g_stamps, sizeof(unsigned long long) * (n < 64 ? n : 64)));
+  if (int rc = tc_debug_stamps_node16(out_host, n)) return rc;   // entries 32..55: mp_node16.cu
   return tc_debug_stamps_edge(out_host, n);     // entries 0..31 belong to mp_edge.cu
 #else
   (void)out_host; (void)n;

@@ -47,6 +47,7 @@ struct TcBuffers {
 int tc_configure();
 int tc_debug_stamps(unsigned long long* out_host, int n);   // -DGM_STAMPS builds only
 int tc_debug_stamps_edge(unsigned long long* out_host, int n);
+int tc_debug_stamps_node16(unsigned long long* out_host, int n);
 int tc_enc_edge(const TcMlp& m, int edge_dim, const float* pos, int pos_stride, float conn_r,
                 const float* edge_attr /*optional explicit [E,edge_dim] in receiver-major order*/,
                 const int* eref /*optional: row map into edge_attr*/, const TcGraph& g, const TcBuffers& b,

@@ -21,5 +21,9 @@ print("edge compute deltas:", [int(s[i + 1] - s[i]) for i in range(15)])
 print("edge E1 fine stamps (since stamp 5: ld0 done, blk0, blk1, blk2, blk3, published, issued):", [int(x - s[5]) for x in s[16:23]])
 print("edge LN fine stamps (since stamp 2: acc loaded, mean, rstd; stamp 10 = rows stored):", [int(x - s[2]) for x in (s[25], s[26], s[27], s[10])])
 print("edge pdl wait (cycles):", int(s[24] - s[23]))
-print("node stamps:", [int(x - s[32]) for x in s[32:44]])
+names_n = ["v rows -> operand", "publish + issue 1b", "GEMM 1b", "weights + pdl_wait", "agg rows -> operand", "publish + issue 1a", "GEMM 1a",
+           "residual copy + epilogue 1", "publish + issue 2", "GEMM 2", "epilogue 2", "publish + issue 3", "GEMM 3", "LayerNorm + operand",
+           "publish + issue Wr", "v' rows out", "GEMM Wr", "Pr staged", "publish + issue Ws", "Pr out + GEMM Ws", "Ps staged", "Ps out"]
+sn = s[32:55]
+print("mp_node16 phase deltas:", {names_n[i]: int(sn[i + 1] - sn[i]) for i in range(22)}, "tile:", int(sn[22] - sn[0]))
 print("node_finish stamps (since 44: ln, a0, launch Wr, copy v, wait, stage Pr, launch Ws, wait, stage Ps, copy Ps):", [int(x - s[44]) for x in s[45:55]])
