@@ -25,6 +25,7 @@ constexpr uint32_t kIdesc16 = umma_idesc_bf16(kTile, kH);
 struct Misc16 {
   uint64_t bar_w;
   uint64_t bar_mma;
+  uint64_t bar_w2;                            // the second weight chunk of a tile's first layer, loaded up front into A0
   uint32_t tmem_base;
   uint32_t pad;
   alignas(16) float red[2][4][kTile];         // [statistic][column quarter][row]
@@ -39,7 +40,7 @@ struct Ctx16 {
   char *A0, *T, *W;
   uint32_t a0_s, t_s, w_s;
   Misc16* misc;
-  uint32_t bar_w, bar_mma, tmem, ph_w, ph_mma;
+  uint32_t bar_w, bar_mma, tmem, ph_w, ph_mma, bar_w2, ph_w2;
   int tid, lane, warp, q, cq, row, col0;
 };
 
@@ -61,25 +62,27 @@ __device__ __forceinline__ void store_a8_16(char* a, int row, int col, const flo
   *reinterpret_cast<uint4*>(a + kImageBytes + o) = lo;
 }
 
-__device__ __forceinline__ void load_w16(const Ctx16& c, const void* chunk) {
+__device__ __forceinline__ void load_w16_to(const Ctx16& c, const void* chunk, uint32_t dst_s, uint32_t bar) {
   if (c.warp == 0 && c.lane == 0) {
-    mbar_expect_tx(c.bar_w, kChunkBytes);
+    mbar_expect_tx(bar, kChunkBytes);
 #pragma unroll
     for (int i = 0; i < 4; ++i)
-      bulk_g2s(c.w_s + i * kKBlockBytes, (const char*)chunk + (size_t)i * kKBlockBytes, kKBlockBytes, c.bar_w);
+      bulk_g2s(dst_s + i * kKBlockBytes, (const char*)chunk + (size_t)i * kKBlockBytes, kKBlockBytes, bar);
   }
   __syncwarp();
 }
+__device__ __forceinline__ void load_w16(const Ctx16& c, const void* chunk) { load_w16_to(c, chunk, c.w_s, c.bar_w); }
 
 // all threads: publish the operand in buffer `a_s`, then thread 0 waits for the weights and issues the 24 MMAs
-__device__ __forceinline__ void launch_gemm16(Ctx16& c, uint32_t a_s, bool accumulate) {
+// (alt_w: the weights are the chunk that was loaded into A0 on bar_w2 instead of the streamed one in W)
+__device__ __forceinline__ void launch_gemm16(Ctx16& c, uint32_t a_s, bool accumulate, bool alt_w = false) {
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   if (c.warp == 0 && c.lane == 0) {              // (warp-uniform test first: the MMAs are issued from uniform control flow)
-    mbar_wait(c.bar_w, c.ph_w);
+    mbar_wait(alt_w ? c.bar_w2 : c.bar_w, alt_w ? c.ph_w2 : c.ph_w);
     tc_fence_after();
-    const uint64_t a0 = umma_desc_sw128(a_s), w0 = umma_desc_sw128(c.w_s);   // base descriptors once, one add per MMA operand
+    const uint64_t a0 = umma_desc_sw128(a_s), w0 = umma_desc_sw128(alt_w ? c.a0_s : c.w_s);   // base descriptors once, one add per MMA operand
 #pragma unroll
     for (int kb = 0; kb < 2; ++kb) {
 #pragma unroll
@@ -95,7 +98,8 @@ __device__ __forceinline__ void launch_gemm16(Ctx16& c, uint32_t a_s, bool accum
     umma_commit(c.bar_mma);
   }
   __syncwarp();
-  c.ph_w ^= 1u;
+  if (alt_w) c.ph_w2 ^= 1u;
+  else c.ph_w ^= 1u;
 }
 __device__ __forceinline__ void wait_gemm16(Ctx16& c) {
   mbar_wait(c.bar_mma, c.ph_mma);
@@ -197,10 +201,12 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
   c.col0 = c.cq * 32;
   c.bar_w = smem_u32(&c.misc->bar_w);
   c.bar_mma = smem_u32(&c.misc->bar_mma);
-  c.ph_w = c.ph_mma = 0;
+  c.bar_w2 = smem_u32(&c.misc->bar_w2);
+  c.ph_w = c.ph_mma = c.ph_w2 = 0;
   if (c.tid == 0) {
     mbar_init(c.bar_w, 1);
     mbar_init(c.bar_mma, 1);
+    mbar_init(c.bar_w2, 1);
     fence_mbar_init();
   }
   if (c.warp == 0) {
@@ -225,7 +231,12 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
   GM_N16(0);
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
   bool waited = false;
-  if ((int)blockIdx.x < n_tiles) load_w16(c, m.wc[1]);
+  // both weight chunks of layer 1 up front: W1b (node part) into W, W1a (aggregate part) into A0 -- the aggregate operand
+  // is built in T once the node-part GEMM has read the v operand out of it
+  if ((int)blockIdx.x < n_tiles) {
+    load_w16(c, m.wc[1]);
+    load_w16_to(c, m.wc[0], c.a0_s, c.bar_w2);
+  }
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
@@ -240,57 +251,53 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
     const int rp = __ldg(g.recv_ptr + min(node0 + c.warp * kR16 + min(c.lane, kR16), g.n_nodes));
     wait_gemm16(c);
     GM_N16(3);
-    load_w16(c, m.wc[0]);
+    load_w16(c, m.wc[2]);                          // W is free: layer 2's weights stream in under the aggregate phase
     if (!waited) {
       pdl_wait();                                  // aggpart / carry of this step's edge kernel are complete from here on
       pdl_launch_dependents();
       waited = true;
     }
     GM_N16(4);
-    // ---- aggregate per node (first-tile partial + carries of the following 64-row blocks) -> A0 ----
-    // Four rows at a time with every load issued before the first use: the partial row and the first two carries
-    // (a receiver's segment rarely spans more than three 64-row blocks) are independent predicated loads, not a
-    // data-dependent loop per row; summation order as before (partial, then the carries in block order).
+    // ---- aggregate per node (first-tile partial + carries of the following 64-row blocks) -> T ----
+    // All eight rows of the warp with every load issued before the first use: the partial row and the first carry (a
+    // receiver's segment rarely spans more than two 64-row blocks) are independent predicated loads, not a data-dependent
+    // loop per row; summation order as before (partial, then the carries in block order).
+    {
+      float4 x[kR16], c1[kR16];
+      int t0[kR16], t1[kR16];
 #pragma unroll
-    for (int i0 = 0; i0 < kR16; i0 += 4) {
-      float4 x[4], c1[4], c2[4];
-      int t0[4], t1[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int r = c.warp * kR16 + i0 + i;
-        const int sb = __shfl_sync(0xffffffffu, rp, i0 + i);
-        int se = __shfl_sync(0xffffffffu, rp, i0 + i + 1);
+      for (int i = 0; i < kR16; ++i) {
+        const int r = c.warp * kR16 + i;
+        const int sb = __shfl_sync(0xffffffffu, rp, i);
+        int se = __shfl_sync(0xffffffffu, rp, i + 1);
         if (r >= rows_valid) se = sb;
         const bool any = se > sb;
         t0[i] = sb / kAggRows;
         t1[i] = any ? (se - 1) / kAggRows : t0[i] - 1;      // t1 - t0 = number of carries; -1: no edges at all
-        x[i] = c1[i] = c2[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        x[i] = c1[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (any) x[i] = __ldg(reinterpret_cast<const float4*>(b.aggpart + (size_t)(node0 + r) * kH) + c.lane);
         if (t1[i] >= t0[i] + 1) c1[i] = __ldg(reinterpret_cast<const float4*>(b.carry + (size_t)(t0[i] + 1) * kH) + c.lane);
-        if (t1[i] >= t0[i] + 2) c2[i] = __ldg(reinterpret_cast<const float4*>(b.carry + (size_t)(t0[i] + 2) * kH) + c.lane);
       }
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
+      for (int i = 0; i < kR16; ++i) {
         if (t1[i] >= t0[i] + 1) { x[i].x += c1[i].x; x[i].y += c1[i].y; x[i].z += c1[i].z; x[i].w += c1[i].w; }
-        if (t1[i] >= t0[i] + 2) { x[i].x += c2[i].x; x[i].y += c2[i].y; x[i].z += c2[i].z; x[i].w += c2[i].w; }
-        for (int t = t0[i] + 3; t <= t1[i]; ++t) {
+        for (int t = t0[i] + 2; t <= t1[i]; ++t) {
           const float4 y = __ldg(reinterpret_cast<const float4*>(b.carry + (size_t)t * kH) + c.lane);
           x[i].x += y.x; x[i].y += y.y; x[i].z += y.z; x[i].w += y.w;
         }
         uint2 hi, lo;
         split_bf16x2(x[i].x, x[i].y, hi.x, lo.x);
         split_bf16x2(x[i].z, x[i].w, hi.y, lo.y);
-        const uint32_t o = a_off16(c.warp * kR16 + i0 + i, 4 * c.lane);
-        *reinterpret_cast<uint2*>(c.A0 + o) = hi;
-        *reinterpret_cast<uint2*>(c.A0 + kImageBytes + o) = lo;
+        const uint32_t o = a_off16(c.warp * kR16 + i, 4 * c.lane);
+        *reinterpret_cast<uint2*>(c.T + o) = hi;
+        *reinterpret_cast<uint2*>(c.T + kImageBytes + o) = lo;
       }
     }
     GM_N16(5);
-    launch_gemm16(c, c.a0_s, true);                // D += agg W1a^T
+    launch_gemm16(c, c.t_s, true, /*alt_w=*/true);   // D += agg W1a^T (weights in A0)
     GM_N16(6);
     wait_gemm16(c);
     GM_N16(7);
-    load_w16(c, m.wc[2]);
     {                                              // T is free: the fp32 residual rows travel into it meanwhile
       const float* v_in = b.v;
 #pragma unroll
@@ -409,7 +416,10 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
     }
     tc_fence_before();
     __syncthreads();                               // T, A0, dot[] and D are reused by the next tile
-    if (tile + (int)gridDim.x < n_tiles) load_w16(c, m.wc[1]);
+    if (tile + (int)gridDim.x < n_tiles) {
+      load_w16(c, m.wc[1]);
+      load_w16_to(c, m.wc[0], c.a0_s, c.bar_w2);
+    }
   }
   if (!waited) {
     pdl_wait();
