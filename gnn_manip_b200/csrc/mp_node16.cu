@@ -17,8 +17,9 @@ namespace gm {
 
 namespace {
 
-constexpr int NT16 = 512;
-constexpr int kW16 = NT16 / 32;               // 16 warps
+constexpr int kWorkers16 = 512;              // 16 worker warps: (lane quadrant q = warp & 3) x (column quarter cq = warp >> 2)
+constexpr int NT16 = kWorkers16 + 32;         // + warp 16: streams the weights and issues every MMA (see issuer16)
+constexpr int kW16 = kWorkers16 / 32;         // 16 warps
 constexpr int kR16 = kTile / kW16;            // 8 rows per warp in the row-wise phases
 constexpr uint32_t kIdesc16 = umma_idesc_bf16(kTile, kH);
 
@@ -62,44 +63,40 @@ __device__ __forceinline__ void store_a8_16(char* a, int row, int col, const flo
   *reinterpret_cast<uint4*>(a + kImageBytes + o) = lo;
 }
 
-__device__ __forceinline__ void load_w16_to(const Ctx16& c, const void* chunk, uint32_t dst_s, uint32_t bar) {
-  if (c.warp == 0 && c.lane == 0) {
-    mbar_expect_tx(bar, kChunkBytes);
+// issuer lane: one 64 KB weight chunk -> dst_s, completion on `bar`
+__device__ __forceinline__ void load_w16_to(const void* chunk, uint32_t dst_s, uint32_t bar) {
+  mbar_expect_tx(bar, kChunkBytes);
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-      bulk_g2s(dst_s + i * kKBlockBytes, (const char*)chunk + (size_t)i * kKBlockBytes, kKBlockBytes, bar);
-  }
-  __syncwarp();
+  for (int i = 0; i < 4; ++i)
+    bulk_g2s(dst_s + i * kKBlockBytes, (const char*)chunk + (size_t)i * kKBlockBytes, kKBlockBytes, bar);
 }
-__device__ __forceinline__ void load_w16(const Ctx16& c, const void* chunk) { load_w16_to(c, chunk, c.w_s, c.bar_w); }
 
 // all threads: publish the operand in buffer `a_s`, then thread 0 waits for the weights and issues the 24 MMAs
-// (alt_w: the weights are the chunk that was loaded into A0 on bar_w2 instead of the streamed one in W)
-__device__ __forceinline__ void launch_gemm16(Ctx16& c, uint32_t a_s, bool accumulate, bool alt_w = false) {
+// workers: the operand of the next GEMM is complete (their generic-proxy writes made visible to the async proxy); the
+// issuer warp takes it from the barrier on
+__device__ __forceinline__ void publish16() {
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
-  if (c.warp == 0 && c.lane == 0) {              // (warp-uniform test first: the MMAs are issued from uniform control flow)
-    mbar_wait(alt_w ? c.bar_w2 : c.bar_w, alt_w ? c.ph_w2 : c.ph_w);
-    tc_fence_after();
-    const uint64_t a0 = umma_desc_sw128(a_s), w0 = umma_desc_sw128(alt_w ? c.a0_s : c.w_s);   // base descriptors once, one add per MMA operand
+}
+__device__ __forceinline__ void sync_workers16() { named_bar_sync(5, kWorkers16); }   // (ids 1..4: the LayerNorm quadrants)
+
+// issuer (lane 0 of warp 16): the 24 MMAs of one GEMM, A images at a_s, weight chunk at w_s
+__device__ __forceinline__ void issue_gemm16(const Ctx16& c, uint32_t a_s, uint32_t w_s, bool accumulate) {
+  const uint64_t a0 = umma_desc_sw128(a_s), w0 = umma_desc_sw128(w_s);   // base descriptors once, one add per MMA operand
 #pragma unroll
-    for (int kb = 0; kb < 2; ++kb) {
+  for (int kb = 0; kb < 2; ++kb) {
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks) {
-        const uint32_t off = kb * kKBlockBytes + ks * 32;
-        const uint64_t ah = umma_desc_advance(a0, off), al = umma_desc_advance(a0, kImageBytes + off);
-        const uint64_t wh = umma_desc_advance(w0, off), wl = umma_desc_advance(w0, kImageBytes + off);
-        umma_bf16_ss(c.tmem, ah, wh, kIdesc16, (accumulate || kb || ks) ? 1u : 0u);
-        umma_bf16_ss(c.tmem, ah, wl, kIdesc16, 1u);
-        umma_bf16_ss(c.tmem, al, wh, kIdesc16, 1u);
-      }
+    for (int ks = 0; ks < 4; ++ks) {
+      const uint32_t off = kb * kKBlockBytes + ks * 32;
+      const uint64_t ah = umma_desc_advance(a0, off), al = umma_desc_advance(a0, kImageBytes + off);
+      const uint64_t wh = umma_desc_advance(w0, off), wl = umma_desc_advance(w0, kImageBytes + off);
+      umma_bf16_ss(c.tmem, ah, wh, kIdesc16, (accumulate || kb || ks) ? 1u : 0u);
+      umma_bf16_ss(c.tmem, ah, wl, kIdesc16, 1u);
+      umma_bf16_ss(c.tmem, al, wh, kIdesc16, 1u);
     }
-    umma_commit(c.bar_mma);
   }
-  __syncwarp();
-  if (alt_w) c.ph_w2 ^= 1u;
-  else c.ph_w ^= 1u;
+  umma_commit(c.bar_mma);
 }
 __device__ __forceinline__ void wait_gemm16(Ctx16& c) {
   mbar_wait(c.bar_mma, c.ph_mma);
@@ -231,12 +228,55 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
   GM_N16(0);
   const int n_tiles = (g.n_nodes + kTile - 1) / kTile;
   bool waited = false;
-  // both weight chunks of layer 1 up front: W1b (node part) into W, W1a (aggregate part) into A0 -- the aggregate operand
-  // is built in T once the node-part GEMM has read the v operand out of it
-  if ((int)blockIdx.x < n_tiles) {
-    load_w16(c, m.wc[1]);
-    load_w16_to(c, m.wc[0], c.a0_s, c.bar_w2);
-  }
+  if (c.warp == kW16) {
+    // ---------------- issuer warp: streams the weight chunks and issues every MMA, so that no worker warp is held up
+    // by the issue of a GEMM (the workers copy rows out while the GEMMs of the tail run).  GEMMs of a tile in order:
+    // 0 v W1b^T, 1 agg W1a^T (accumulating), 2 layer 2, 3 layer 3, 4 Wr | decoder 1, 5 Ws | decoder 2.
+    // Both chunks of layer 1 are loaded up front: W1b into W, W1a into A0 (the aggregate operand is built in T once GEMM 0
+    // has read the v operand out of it); every other chunk goes into W as soon as the GEMM before it has completed.
+    // (wait-then-trigger like the workers: one early griddepcontrol.launch_dependents from this warp would release the
+    // next edge kernel before this step's edge kernel has finished writing the rows its prologue reads)
+    bool triggered = false;
+    const void* x1 = has_dec ? next.wc[0] : next.wc[3];
+    const void* x2 = has_dec ? next.wc[1] : next.wc[4];
+    uint32_t ph_w = 0, ph_w2 = 0, ph_mma = 0;
+    if (c.lane == 0 && (int)blockIdx.x < n_tiles) {
+      load_w16_to(m.wc[1], c.w_s, c.bar_w);
+      load_w16_to(m.wc[0], c.a0_s, c.bar_w2);
+    }
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+#pragma unroll 1
+      for (int gi = 0; gi < 6; ++gi) {
+        __syncthreads();                           // the workers' publish16(): operand gi is complete
+        if (c.lane == 0) {
+          const bool alt = gi == 1;
+          mbar_wait(alt ? c.bar_w2 : c.bar_w, alt ? ph_w2 : ph_w);
+          if (alt) ph_w2 ^= 1u;
+          else ph_w ^= 1u;
+          tc_fence_after();
+          issue_gemm16(c, gi < 2 ? c.t_s : c.a0_s, alt ? c.a0_s : c.w_s, gi == 1);
+          mbar_wait(c.bar_mma, ph_mma);            // GEMM gi complete: its weight buffer is free
+          ph_mma ^= 1u;
+          if (!triggered) {
+            pdl_wait();
+            pdl_launch_dependents();
+            triggered = true;
+          }
+          const void* nxt = gi == 0 ? m.wc[2] : gi == 2 ? m.wc[3] : gi == 3 ? x1 : gi == 4 ? x2 : nullptr;
+          if (nxt != nullptr) load_w16_to(nxt, c.w_s, c.bar_w);
+          if (gi == 5 && tile + (int)gridDim.x < n_tiles) {
+            load_w16_to(m.wc[1], c.w_s, c.bar_w);
+            load_w16_to(m.wc[0], c.a0_s, c.bar_w2);
+          }
+        }
+        __syncwarp();
+      }
+    }
+    if (!triggered) {
+      pdl_wait();
+      pdl_launch_dependents();
+    }
+  } else {
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int node0 = tile * kTile;
     const int rows_valid = min(kTile, g.n_nodes - node0);
@@ -246,12 +286,11 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
       rows_to_a16(c, c.T, rows_valid, [=](int r) { return v_in + (size_t)(node0 + r) * kH; });
     }
     GM_N16(1);
-    launch_gemm16(c, c.t_s, false);
+    publish16();
     GM_N16(2);
     const int rp = __ldg(g.recv_ptr + min(node0 + c.warp * kR16 + min(c.lane, kR16), g.n_nodes));
     wait_gemm16(c);
     GM_N16(3);
-    load_w16(c, m.wc[2]);                          // W is free: layer 2's weights stream in under the aggregate phase
     if (!waited) {
       pdl_wait();                                  // aggpart / carry of this step's edge kernel are complete from here on
       pdl_launch_dependents();
@@ -294,7 +333,7 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
       }
     }
     GM_N16(5);
-    launch_gemm16(c, c.t_s, true, /*alt_w=*/true);   // D += agg W1a^T (weights in A0)
+    publish16();   // D += agg W1a^T (weights in A0)
     GM_N16(6);
     wait_gemm16(c);
     GM_N16(7);
@@ -310,19 +349,17 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
     }
     epi_hidden16(c, prm + kQB1);
     GM_N16(8);
-    launch_gemm16(c, c.a0_s, false);               // layer 2
+    publish16();               // layer 2
     GM_N16(9);
     wait_gemm16(c);
     GM_N16(10);
-    load_w16(c, m.wc[3]);
     epi_hidden16(c, prm + kQB2);
     cp_async_wait_all();
     GM_N16(11);
-    launch_gemm16(c, c.a0_s, false);               // layer 3 (its barrier also publishes the residual rows in T)
+    publish16();               // layer 3 (its barrier also publishes the residual rows in T)
     GM_N16(12);
     wait_gemm16(c);
     GM_N16(13);
-    load_w16(c, has_dec ? next.wc[0] : next.wc[3]);
     // ---- LayerNorm + residual: v' -> T (fp32) and A0 (operand) ----
     {
       float x[32];
@@ -363,34 +400,32 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
       for (int g8 = 0; g8 < 4; ++g8) store_a8_16(c.A0, c.row, c.col0 + 8 * g8, x + 8 * g8);
     }
     GM_N16(14);
-    launch_gemm16(c, c.a0_s, false);               // v' Wr^T   |   decoder layer 1
+    publish16();               // v' Wr^T   |   decoder layer 1
     GM_N16(15);
     stage_out16(c, b.v, node0, rows_valid);        // v' rows leave while the GEMM runs
     GM_N16(16);
     wait_gemm16(c);
     GM_N16(17);
     if (!has_dec) {
-      load_w16(c, next.wc[4]);
-      __syncthreads();                             // every warp is done reading v' out of T
+      sync_workers16();                            // every warp is done reading v' out of T
       acc_to_stage16(c, next.b1);                  // Pr carries b1 of the next edge MLP (mp_edge.cu adds no bias)
       GM_N16(18);
-      launch_gemm16(c, c.a0_s, false);             // v' Ws^T (the barrier inside publishes T)
+      publish16();             // v' Ws^T (the barrier inside publishes T)
       GM_N16(19);
       stage_out16(c, b.pr, node0, rows_valid);
       wait_gemm16(c);
       GM_N16(20);
-      __syncthreads();
+      sync_workers16();
       acc_to_stage16(c, nullptr);
       tc_fence_before();
-      __syncthreads();
+      sync_workers16();
       GM_N16(21);
       stage_out16(c, b.ps, node0, rows_valid);
       GM_N16(22);
     } else {
       // decoder: Linear+ReLU, Linear+ReLU on the tensor cores, Linear(128 -> out_dim) on CUDA cores (epd_gnn.py:49, 96)
-      load_w16(c, next.wc[1]);
       epi_hidden16(c, prm + kQD1);
-      launch_gemm16(c, c.a0_s, false);
+      publish16();
       wait_gemm16(c);
       float acc[3] = {0.f, 0.f, 0.f};
       {
@@ -406,7 +441,7 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
 #pragma unroll
       for (int o = 0; o < 3; ++o) c.misc->dot[o][c.cq][c.row] = acc[o];
       tc_fence_before();
-      __syncthreads();
+      sync_workers16();
       if (c.cq == 0 && c.row < rows_valid) {
         for (int o = 0; o < out_dim; ++o) {
           const float* d = &c.misc->dot[o][0][c.row];
@@ -415,15 +450,12 @@ mp_node16_kernel(TcMlp m, TcMlp next, int has_dec, int out_dim, float* __restric
       }
     }
     tc_fence_before();
-    __syncthreads();                               // T, A0, dot[] and D are reused by the next tile
-    if (tile + (int)gridDim.x < n_tiles) {
-      load_w16(c, m.wc[1]);
-      load_w16_to(c, m.wc[0], c.a0_s, c.bar_w2);
-    }
+    sync_workers16();                              // T, dot[] and D are reused by the next tile
   }
   if (!waited) {
     pdl_wait();
     pdl_launch_dependents();
+  }
   }
   tc_fence_before();
   __syncthreads();
