@@ -820,6 +820,13 @@ __device__ __forceinline__ void split_pair(float2 x, uint32_t& hi, uint32_t& lo)
   __nv_bfloat162 l = __floats2bfloat162_rn(r.x, r.y);
   lo = *reinterpret_cast<uint32_t*>(&l);
 }
+__device__ __forceinline__ void put_operand32_p(const float2* v, uint32_t tAH, uint32_t tAL, int c32) {
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) split_pair(v[j], hi[j], lo[j]);
+  tmem_st16(tAH + c32 * 16, hi);
+  tmem_st16(tAL + c32 * 16, lo);
+}
 __device__ __forceinline__ void put_operand32_inplace_p(const float2* v, uint32_t tR, int c32) {
   uint32_t hi[16], lo[16];
 #pragma unroll
@@ -1281,8 +1288,10 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
   extern __shared__ __align__(1024) char smem_raw[];
   char* base = smem_raw;
   const uint32_t W_s = smem_u32(base);
-  float4* w1s = reinterpret_cast<float4*>(base + 2 * kWLayer);          // [128] rows of the 4-wide first layer
-  float* b1s = reinterpret_cast<float*>(base + 2 * kWLayer + kH * 16);  // [128]
+  // first layer (4 -> 128), stored for PAIRS of outputs (a, b) = (2p, 2p + 1): w1p[8 p ..] = {wa.x, wb.x, wa.y, wb.y, wa.z,
+  // wb.z, wa.w, wb.w}, so that two float4 loads give the operands of four packed FMAs (f2_fma) for both outputs
+  float* w1p = reinterpret_cast<float*>(base + 2 * kWLayer);             // [64][8]
+  float* b1s = reinterpret_cast<float*>(base + 2 * kWLayer + kH * 16);   // [128]
   char* S_base = base + kWBytes;
   EdgeShared* sh = reinterpret_cast<EdgeShared*>(S_base + 2 * kStageBytes);
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // (warp-uniform)
@@ -1306,7 +1315,8 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
     sh->prm[kOffB3 + i] = m.b3[i];
     sh->prm[kOffG + i] = m.ln_g[i];
     sh->prm[kOffBeta + i] = m.ln_b[i];
-    w1s[i] = make_float4(m.w1[4 * i], m.w1[4 * i + 1], m.w1[4 * i + 2], m.w1[4 * i + 3]);
+#pragma unroll
+    for (int k4 = 0; k4 < 4; ++k4) w1p[(i >> 1) * 8 + 2 * k4 + (i & 1)] = m.w1[4 * i + k4];
     b1s[i] = m.b1[i];
   }
   tc_fence_before();
@@ -1357,13 +1367,18 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
   auto layer1 = [&](const float4& x) {
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      float v[32];
+      float2 v[16];
+      const float2 xx = make_float2(x.x, x.x), xy = make_float2(x.y, x.y), xz = make_float2(x.z, x.z), xw = make_float2(x.w, x.w);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float4 w = w1s[c * 32 + j];
-        v[j] = fmaxf(fmaf(x.w, w.w, fmaf(x.z, w.z, fmaf(x.y, w.y, fmaf(x.x, w.x, b1s[c * 32 + j])))), 0.f);
+      for (int j = 0; j < 16; ++j) {
+        const float4 w01 = *reinterpret_cast<const float4*>(w1p + (c * 16 + j) * 8);
+        const float4 w23 = *reinterpret_cast<const float4*>(w1p + (c * 16 + j) * 8 + 4);
+        const float2 bb = *reinterpret_cast<const float2*>(b1s + c * 32 + 2 * j);
+        // per output: fma(x.w, w.w, fma(x.z, w.z, fma(x.y, w.y, fma(x.x, w.x, b)))) -- the SIMT path's order
+        v[j] = f2_relu(f2_fma(xw, make_float2(w23.z, w23.w), f2_fma(xz, make_float2(w23.x, w23.y),
+                       f2_fma(xy, make_float2(w01.z, w01.w), f2_fma(xx, make_float2(w01.x, w01.y), bb)))));
       }
-      put_operand32(v, tAH, tAL, c);
+      put_operand32_p(v, tAH, tAL, c);
     }
   };
   float4 xn = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1387,27 +1402,25 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
     ph_d ^= 1u;
     tc_fence_after();
     {
-      float va[32], vb[32];
-      auto e2_block = [&](int c, float* v) {
+      float2 va[16], vb[16];
+      auto e2_block = [&](int c, float2* v) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float4 bs = GM_PRM4(prm + kOffB2 + c * 32 + 4 * j);
-          v[4 * j] = fmaxf(v[4 * j] + bs.x, 0.f);
-          v[4 * j + 1] = fmaxf(v[4 * j + 1] + bs.y, 0.f);
-          v[4 * j + 2] = fmaxf(v[4 * j + 2] + bs.z, 0.f);
-          v[4 * j + 3] = fmaxf(v[4 * j + 3] + bs.w, 0.f);
+          v[2 * j] = f2_relu(f2_add(v[2 * j], make_float2(bs.x, bs.y)));
+          v[2 * j + 1] = f2_relu(f2_add(v[2 * j + 1], make_float2(bs.z, bs.w)));
         }
-        put_operand32(v, tAH, tAL, c);
+        put_operand32_p(v, tAH, tAL, c);
       };
-      tmem_ld32(tD, va);
+      tmem_ld32(tD, reinterpret_cast<float*>(va));
       tmem_ld_wait();
-      tmem_ld32(tD + 32, vb);
+      tmem_ld32(tD + 32, reinterpret_cast<float*>(vb));
       e2_block(0, va);
       tmem_ld_wait();
-      tmem_ld32(tD + 64, va);
+      tmem_ld32(tD + 64, reinterpret_cast<float*>(va));
       e2_block(1, vb);
       tmem_ld_wait();
-      tmem_ld32(tD + 96, vb);
+      tmem_ld32(tD + 96, reinterpret_cast<float*>(vb));
       e2_block(2, va);
       tmem_ld_wait();
       e2_block(3, vb);
@@ -1422,34 +1435,40 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
     // under this tile's LayerNorm and row stores once every warp has the accumulator in registers
     if (has_next) layer1(x_next);
     {
-      float y[kH];
+      // exact two-pass LayerNorm of the whole row in registers, packed fp32 arithmetic (same operations per element)
+      float2 y[kH / 2];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld32(tD + c * 32, y + c * 32);
+      for (int c = 0; c < 4; ++c) tmem_ld32(tD + c * 32, reinterpret_cast<float*>(y) + c * 32);
       tmem_ld_wait();
       if (has_next) publish_operand(bar_a, lane);
-      float sa = 0.f, sb = 0.f, sc = 0.f, sd = 0.f;
+      float2 sab = make_float2(0.f, 0.f), scd = sab;
 #pragma unroll
       for (int j = 0; j < kH / 4; ++j) {
         const float4 t = GM_PRM4(prm + kOffB3 + 4 * j);
-        y[4 * j] += t.x; y[4 * j + 1] += t.y; y[4 * j + 2] += t.z; y[4 * j + 3] += t.w;
-        sa += y[4 * j]; sb += y[4 * j + 1]; sc += y[4 * j + 2]; sd += y[4 * j + 3];
+        y[2 * j] = f2_add(y[2 * j], make_float2(t.x, t.y));
+        y[2 * j + 1] = f2_add(y[2 * j + 1], make_float2(t.z, t.w));
+        sab = f2_add(sab, y[2 * j]);
+        scd = f2_add(scd, y[2 * j + 1]);
       }
-      const float mean = ((sa + sb) + (sc + sd)) * (1.0f / kH);
-      float qa = 0.f, qb = 0.f, qc = 0.f, qd = 0.f;
+      const float mean = ((sab.x + sab.y) + (scd.x + scd.y)) * (1.0f / kH);
+      const float2 mean2 = make_float2(mean, mean);
+      float2 qab = make_float2(0.f, 0.f), qcd = qab;
 #pragma unroll
       for (int j = 0; j < kH / 4; ++j) {
-        y[4 * j] -= mean; y[4 * j + 1] -= mean; y[4 * j + 2] -= mean; y[4 * j + 3] -= mean;
-        qa = fmaf(y[4 * j], y[4 * j], qa); qb = fmaf(y[4 * j + 1], y[4 * j + 1], qb);
-        qc = fmaf(y[4 * j + 2], y[4 * j + 2], qc); qd = fmaf(y[4 * j + 3], y[4 * j + 3], qd);
+        y[2 * j] = f2_sub(y[2 * j], mean2);
+        y[2 * j + 1] = f2_sub(y[2 * j + 1], mean2);
+        qab = f2_fma(y[2 * j], y[2 * j], qab);
+        qcd = f2_fma(y[2 * j + 1], y[2 * j + 1], qcd);
       }
-      const float rstd = 1.0f / sqrtf(((qa + qb) + (qc + qd)) * (1.0f / kH) + 1e-5f);
+      const float rstd = 1.0f / sqrtf(((qab.x + qab.y) + (qcd.x + qcd.y)) * (1.0f / kH) + 1e-5f);
+      const float2 rstd2 = make_float2(rstd, rstd);
 #pragma unroll
       for (int j = 0; j < kH / 4; ++j) {
         const float4 g4 = GM_PRM4(prm + kOffG + 4 * j);
         const float4 b4 = GM_PRM4(prm + kOffBeta + 4 * j);
-        *reinterpret_cast<float4*>(S + (j >> 3) * kBoxBytes + ro[j & 7]) =
-            make_float4(y[4 * j] * rstd * g4.x + b4.x, y[4 * j + 1] * rstd * g4.y + b4.y,
-                        y[4 * j + 2] * rstd * g4.z + b4.z, y[4 * j + 3] * rstd * g4.w + b4.w);
+        const float2 o01 = f2_fma(f2_mul(y[2 * j], rstd2), make_float2(g4.x, g4.y), make_float2(b4.x, b4.y));
+        const float2 o23 = f2_fma(f2_mul(y[2 * j + 1], rstd2), make_float2(g4.z, g4.w), make_float2(b4.z, b4.w));
+        *reinterpret_cast<float4*>(S + (j >> 3) * kBoxBytes + ro[j & 7]) = make_float4(o01.x, o01.y, o23.x, o23.y);
       }
     }
     __syncwarp();
@@ -1458,11 +1477,17 @@ enc_edge_pair_kernel(TcMlp m, const float* __restrict__ pos, int pos_stride, flo
     {
       const int nr = min(32, rows_valid - r0);
       float* e_out = b.e + (size_t)(row0 + r0) * kH + 4 * lane;
+      if (nr >= 32) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          *reinterpret_cast<float4*>(e_out + i * kH) = *reinterpret_cast<const float4*>(S + (db[i & 7] - S_s) + (i & ~7) * 128);
+      } else {
 #pragma unroll 8
-      for (int i = 0; i < 32; ++i)
-        if (i < nr)
-          *reinterpret_cast<float4*>(e_out + i * kH) =
-              *reinterpret_cast<const float4*>(S + (db[i & 7] - S_s) + (i & ~7) * 128);
+        for (int i = 0; i < 32; ++i)
+          if (i < nr)
+            *reinterpret_cast<float4*>(e_out + i * kH) =
+                *reinterpret_cast<const float4*>(S + (db[i & 7] - S_s) + (i & ~7) * 128);
+      }
     }
     __syncwarp();                                  // the rows are rewritten by this warp's next tile
   }
