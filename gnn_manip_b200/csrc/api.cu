@@ -147,6 +147,7 @@ int trace_dump_physics(unsigned long long*, int);
 int trace_dump_radius(unsigned long long*, int);
 int trace_dump_tc(unsigned long long*, int);
 int trace_dump_edge(unsigned long long*, int);
+int trace_dump_node16(unsigned long long*, int);
 }
 #endif
 
@@ -1078,8 +1079,10 @@ int gm_adam_step(float* params, const float* grads, float* m, float* v, size_t n
 int gm_debug_stamps(unsigned long long* out_host, int32_t n) {
   if (n < 4 * 161) return GM_ERR_UNSUPPORTED;
   cudaDeviceSynchronize();
-  int (*fn[4])(unsigned long long*, int) = {gm::trace_dump_physics, gm::trace_dump_radius, gm::trace_dump_tc, gm::trace_dump_edge};
-  for (int i = 0; i < 4; ++i) out_host[i * 161] = (unsigned long long)fn[i](out_host + i * 161 + 1, 160);
+  int (*fn[5])(unsigned long long*, int) = {gm::trace_dump_physics, gm::trace_dump_radius, gm::trace_dump_tc, gm::trace_dump_edge,
+                                            gm::trace_dump_node16};
+  const int nf = n >= 5 * 161 ? 5 : 4;          // (a fifth block, mp_node16.cu, for callers that pass room for it)
+  for (int i = 0; i < nf; ++i) out_host[i * 161] = (unsigned long long)fn[i](out_host + i * 161 + 1, 160);
   return GM_OK;
 }
 #else

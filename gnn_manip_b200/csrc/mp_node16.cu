@@ -495,4 +495,6 @@ int tc_mp_node16(const TcMlp& m, const TcMlp* next_edge, const TcMlp* dec, int o
   return GM_OK;
 }
 
+GM_TRACE_DUMP(trace_dump_node16)
+
 }  // namespace gm

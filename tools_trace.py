@@ -14,12 +14,12 @@ rot = np.stack([c[0] for c in curves]) if ng > 1 else curves[0][0]
 ty = np.stack([c[1] for c in curves]) if ng > 1 else curves[0][1]
 plan = gm.Rollout(model, bench.make_graph_attr(gm), obs, rot=rot, ty=ty, ty_init=tuple(scenes.TY_INIT),
                   n_graphs=ng, use_cuda_graph=True, impl=gm._lib.GM_IMPL_TC)
-buf = (ctypes.c_ulonglong * (4 * 161))()
-dump = lambda: gm._lib.check(gm._lib.lib().gm_debug_stamps(buf, 4 * 161), "gm_debug_stamps")
+buf = (ctypes.c_ulonglong * (5 * 161))()
+dump = lambda: gm._lib.check(gm._lib.lib().gm_debug_stamps(buf, 5 * 161), "gm_debug_stamps")
 plan.run(12); torch.cuda.synchronize(); dump()
 plan.run(2); torch.cuda.synchronize(); dump()
 s = np.array(buf[:], dtype=np.int64)
-names = ["physics", "radius", "node", "edge"]
+names = ["physics", "radius", "enc_node", "edge", "node"]
 ev = []
 for i, nm in enumerate(names):
     c = int(s[i * 161])
