@@ -10,6 +10,10 @@ echo "edge16 rc=$?"
 C3S="python bench.py --only-c3-step"
 timeout 120 $C3S > gpurun_out/plain_c3step.log 2>&1 && timeout 400 ncu --set full --clock-control none --import-source on -k regex:neighbour_kernel -s 1 -c 1 -f -o gpurun_out/prof_neighbour_final $C3S > gpurun_out/ncu_nb.log 2>&1
 echo "neighbour rc=$?"
+timeout 400 ncu --set full --clock-control none --import-source on -k regex:mp_node16 -s 4 -c 1 -f -o gpurun_out/prof_mp_node16_final $C3 > gpurun_out/ncu_node.log 2>&1
+echo "node16 rc=$?"
+timeout 400 ncu --set full --clock-control none --import-source on -k regex:enc_edge_pair -s 1 -c 1 -f -o gpurun_out/prof_enc_edge_final $C3 > gpurun_out/ncu_enc.log 2>&1
+echo "enc_edge rc=$?"
 TR="python tools_train_launches.py"
 timeout 200 $TR > gpurun_out/plain_c5.log 2>&1 && timeout 400 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:tr_gemm --launch-skip 7 -c 1 -f -o gpurun_out/prof_tr_gemm_final $TR > gpurun_out/ncu_gemm.log 2>&1
 echo "tr_gemm rc=$?"
